@@ -1,0 +1,296 @@
+// Chain GADMM / D-GADMM hot loop (K3 + K4 + K5 of SURVEY.md section 2.4) and the batched
+// packed-symmetric SYMV it is built on.
+//
+//   gadmm_half_iter_kernel   one colour (head or tail group) of one iteration:
+//       r_n = b_n - nu_n + rho*(theta_l + theta_r)      (fused into the tile producer)
+//       theta_n = M_n r_n                                (streamed packed-symmetric SYMV)
+//       f_n(theta_n) = 0.5 theta'(r - c rho theta) - b'theta + 0.5 y'y   (no extra matrix pass)
+//       theta_n -> local replica and, over NVLink, into the replicas of the GPUs that own the
+//       chain neighbours, followed by a system-scope release flag
+//     (group_ADMM_closedForm.m:13-57 / :61-92; static_group_ADMM_closedForm.m:50-80)
+//   gadmm_dual_objective_kernel
+//       nu_n += rho(theta_n - theta_r) - rho(theta_l - theta_n)
+//       all-rank objective sum through peer stores + flags, stop test, device clock, iteration++
+//     (static_group_ADMM_closedForm.m:130-160; group_ADMM_closedForm.m:96-108)
+//
+// No NCCL and no host on this path: consumers spin on `flags` with ld.acquire.sys.
+#include "../include/gadmm_b200.h"
+#include "symv_core.cuh"
+
+#include <stdarg.h>
+
+namespace gadmm {
+
+thread_local char g_last_error[512] = {0};
+
+int set_error(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_last_error, sizeof(g_last_error), fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+// ------------------------------------------------------------------------------ plain SYMV
+struct PlainX {
+  const double* x;
+  __device__ __forceinline__ double operator()(int j) const { return x[j]; }
+};
+
+template <typename T>
+__global__ void __launch_bounds__(kSymvThreads, 2)
+symv_batched_kernel(const void* const* __restrict__ Sptr, const double* __restrict__ x,
+                    double* __restrict__ y, int dp, double* __restrict__ scratch,
+                    unsigned int* __restrict__ counters) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  SymvSmem<T>& sm = *reinterpret_cast<SymvSmem<T>*>(smem_raw);
+  const int nT = dp / kT, npairs = (nT + 1) / 2;
+  const int k = blockIdx.x / npairs, p = blockIdx.x % npairs;
+  const size_t per = (size_t)dp + colpart_elems(dp);
+  double* rowpart = scratch + (size_t)k * per;
+  double* colpart = rowpart + dp;
+  PlainX xf{x + (size_t)k * dp};
+  const bool last = symv_cta<T>(sm, reinterpret_cast<const T*>(Sptr[k]), nT, p, xf, rowpart,
+                                colpart, counters + k, npairs);
+  if (!last) return;
+  for (int j = threadIdx.x; j < dp; j += blockDim.x)
+    y[(size_t)k * dp + j] = symv_gather(rowpart, colpart, nT, j);
+}
+
+// -------------------------------------------------------------------------- chain half-iteration
+struct ChainX {
+  const double* b;
+  const double* nu;
+  const double* tl;   // neighbour replicas (may be null at the chain ends)
+  const double* tr;
+  double rho;
+  __device__ __forceinline__ double operator()(int j) const {
+    double t = 0.0;
+    if (tl) t += __ldcg(tl + j);
+    if (tr) t += __ldcg(tr + j);
+    return fma(rho, t, b[j] - nu[j]);
+  }
+};
+
+template <typename T>
+__global__ void __launch_bounds__(kSymvThreads, 2)
+gadmm_half_iter_kernel(const GadmmChain c, const int color) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  SymvSmem<T>& sm = *reinterpret_cast<SymvSmem<T>*>(smem_raw);
+  const int nT = c.dp / kT, npairs = (nT + 1) / 2;
+  const int k = blockIdx.x / npairs, p = blockIdx.x % npairs;
+  if (c.color[k] != color) return;
+  const unsigned long long it = c.ctrl[0];
+  if (c.ctrl[2] != 0ull && c.ctrl[1] != 0ull) return;   // converged: freeze the state
+  if (it > (unsigned long long)c.max_iter) return;
+
+  const int g = c.gid[k], l = c.left[k], r = c.right[k];
+  // heads read the tails' previous iterate, tails read this iteration's heads
+  const unsigned long long need = (color == 0) ? it - 1 : it;
+  const size_t slot_in = (size_t)(need & 1ull) * c.Nglob;
+  if (threadIdx.x == kConsumerWarps * 32) {   // producer lane 0 waits for remote neighbours
+    if (l >= 0 && c.owner[l] != c.rank) wait_flag_ge(c.flags + l, need);
+    if (r >= 0 && c.owner[r] != c.rank) wait_flag_ge(c.flags + r, need);
+  }
+  __syncthreads();
+
+  ChainX xf;
+  xf.b = c.b + (size_t)k * c.dp;
+  xf.nu = c.nu + (size_t)k * c.dp;
+  xf.tl = l >= 0 ? c.theta + (slot_in + l) * c.dp : nullptr;
+  xf.tr = r >= 0 ? c.theta + (slot_in + r) * c.dp : nullptr;
+  xf.rho = c.rho;
+
+  double* rowpart = c.rowpart + (size_t)k * c.dp;
+  double* colpart = c.colpart + (size_t)k * colpart_elems(c.dp);
+  const bool last = symv_cta<T>(sm, reinterpret_cast<const T*>(c.Mptr[k]), nT, p, xf, rowpart,
+                                colpart, c.counters + k, npairs);
+  if (!last) return;
+
+  // ---------------------------------------------------------------- finisher (one CTA per worker)
+  const size_t slot_out = (size_t)(it & 1ull) * c.Nglob;
+  double* th_loc = c.theta + (slot_out + g) * c.dp;
+  const int p0 = c.push0[k], p1 = c.push1[k];
+  double* th_p0 = p0 >= 0 ? c.theta_peer[p0] + (slot_out + g) * c.dp : nullptr;
+  double* th_p1 = p1 >= 0 ? c.theta_peer[p1] + (slot_out + g) * c.dp : nullptr;
+  const double crho = c.rho * (double)c.cmul[k];
+  double s1 = 0.0, s2 = 0.0;
+  for (int j = threadIdx.x; j < c.dp; j += blockDim.x) {
+    const double th = symv_gather(rowpart, colpart, nT, j);
+    const double rj = xf(j);
+    th_loc[j] = th;
+    if (th_p0) th_p0[j] = th;          // NVLink P2P store into the neighbour GPU's replica
+    if (th_p1) th_p1[j] = th;
+    s1 = fma(th, rj - crho * th, s1);  // theta'(G theta) with G theta = r - c rho theta
+    s2 = fma(xf.b[j], th, s2);
+  }
+  double* red = &sm.colbuf[0][0][0];
+  s1 = block_sum(s1, red);
+  s2 = block_sum(s2, red);
+  if (threadIdx.x == 0) {
+    c.objw[k] = 0.5 * s1 - s2 + c.hyy[k];
+    __threadfence_system();
+    if (p0 >= 0) st_release_sys(c.flags_peer[p0] + g, it);
+    if (p1 >= 0) st_release_sys(c.flags_peer[p1] + g, it);
+    c.flags[g] = it;
+  }
+}
+
+// --------------------------------------------------------------------- dual update + objective
+__global__ void __launch_bounds__(256)
+gadmm_dual_objective_kernel(const GadmmChain c) {
+  __shared__ double red[32];
+  __shared__ unsigned int ticket;
+  const unsigned long long it = c.ctrl[0];
+  if (c.ctrl[2] != 0ull && c.ctrl[1] != 0ull) return;
+  if (it > (unsigned long long)c.max_iter) return;
+  const int k = blockIdx.x;
+  const int g = c.gid[k], l = c.left[k], r = c.right[k];
+  if (threadIdx.x == 0) {
+    if (l >= 0 && c.owner[l] != c.rank) wait_flag_ge(c.flags + l, it);
+    if (r >= 0 && c.owner[r] != c.rank) wait_flag_ge(c.flags + r, it);
+  }
+  __syncthreads();
+  const size_t slot = (size_t)(it & 1ull) * c.Nglob;
+  const double* th = c.theta + (slot + g) * c.dp;
+  const double* tl = l >= 0 ? c.theta + (slot + l) * c.dp : nullptr;
+  const double* tr = r >= 0 ? c.theta + (slot + r) * c.dp : nullptr;
+  double* nu = c.nu + (size_t)k * c.dp;
+  for (int j = threadIdx.x; j < c.dp; j += blockDim.x) {
+    const double t = __ldcg(th + j);
+    double upd = 0.0;
+    if (tr) upd = upd + c.rho * (t - __ldcg(tr + j));
+    if (tl) upd = upd - c.rho * (__ldcg(tl + j) - t);
+    nu[j] += upd;
+  }
+  // ---- last CTA: objective, stop test, clock
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) ticket = atomicAdd(c.counters + c.Nloc, 1u);
+  __syncthreads();
+  if (ticket != (unsigned)(c.Nloc - 1)) return;
+  __threadfence();
+  double part = 0.0;
+  for (int i = threadIdx.x; i < c.Nloc; i += blockDim.x) part += __ldcg(c.objw + i);
+  part = block_sum(part, red);
+  if (threadIdx.x == 0) {
+    c.counters[c.Nloc] = 0u;
+    double total = part;
+    if (c.nranks > 1) {
+      const int ring = (int)(it & 3ull) * c.nranks;
+      for (int q = 0; q < c.nranks; ++q) {
+        double* dst = c.objpart_peer[q] + ring + c.rank;
+        *reinterpret_cast<volatile double*>(dst) = part;
+      }
+      __threadfence_system();
+      for (int q = 0; q < c.nranks; ++q) st_release_sys(c.objflag_peer[q] + ring + c.rank, it);
+      total = 0.0;
+      for (int q = 0; q < c.nranks; ++q) {      // same order on every rank -> identical decision
+        wait_flag_ge(c.objflag + ring + q, it);
+        total += *reinterpret_cast<volatile double*>(c.objpart + ring + q);
+      }
+    }
+    const double loss = fabs(total - c.obj0);
+    c.obj_hist[it] = total;
+    c.loss_hist[it] = loss;
+    c.t_hist[it] = globaltimer_ns();
+    if (loss < c.acc && c.ctrl[1] == 0ull) c.ctrl[1] = it;
+    c.ctrl[0] = it + 1ull;
+  }
+}
+
+template <typename T>
+static int configure_half() {
+  GADMM_CUDA_OK(cudaFuncSetAttribute(gadmm_half_iter_kernel<T>,
+                                     cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)sizeof(SymvSmem<T>)));
+  return 0;
+}
+
+template <typename T>
+static int launch_half(const GadmmChain* c, int color, cudaStream_t st) {
+  static bool configured = false;
+  const int smem = (int)sizeof(SymvSmem<T>);
+  if (!configured) {
+    if (int e = configure_half<T>()) return e;
+    configured = true;
+  }
+  const int nT = c->dp / kT, npairs = (nT + 1) / 2;
+  gadmm_half_iter_kernel<T><<<c->Nloc * npairs, kSymvThreads, smem, st>>>(*c, color);
+  GADMM_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace gadmm
+
+using namespace gadmm;
+
+extern "C" {
+
+const char* gadmm_last_error(void) { return g_last_error; }
+int gadmm_version(void) { return 100; }
+
+size_t gadmm_packed_elems(int dp) {
+  const size_t nT = dp / kT;
+  return nT * (nT + 1) / 2 * (size_t)(kT * kT);
+}
+
+size_t gadmm_symv_scratch_elems(int dp) { return (size_t)dp + colpart_elems(dp); }
+
+int gadmm_symv_batched(const void* const* Sptr, const double* x, double* y, int N, int dp,
+                       int store, double* scratch, unsigned int* counters, void* stream) {
+  GADMM_REQUIRE(dp > 0 && dp % kT == 0, "symv: dp=%d must be a positive multiple of 64", dp);
+  GADMM_REQUIRE(store == GADMM_STORE_F64 || store == GADMM_STORE_F32, "symv: bad store %d", store);
+  if (N <= 0) return 0;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int nT = dp / kT, npairs = (nT + 1) / 2;
+  if (store == GADMM_STORE_F64) {
+    const int smem = (int)sizeof(SymvSmem<double>);
+    GADMM_CUDA_OK(cudaFuncSetAttribute(symv_batched_kernel<double>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    symv_batched_kernel<double><<<N * npairs, kSymvThreads, smem, st>>>(Sptr, x, y, dp, scratch,
+                                                                       counters);
+  } else {
+    const int smem = (int)sizeof(SymvSmem<float>);
+    GADMM_CUDA_OK(cudaFuncSetAttribute(symv_batched_kernel<float>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    symv_batched_kernel<float><<<N * npairs, kSymvThreads, smem, st>>>(Sptr, x, y, dp, scratch,
+                                                                      counters);
+  }
+  GADMM_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+int gadmm_chain_half_iter(const GadmmChain* c, int color, void* stream) {
+  GADMM_REQUIRE(c && c->dp > 0 && c->dp % kT == 0, "chain: dp must be a positive multiple of 64");
+  GADMM_REQUIRE(color == 0 || color == 1, "chain: color must be 0 or 1");
+  if (c->Nloc <= 0) return 0;
+  return c->store == GADMM_STORE_F64 ? launch_half<double>(c, color, (cudaStream_t)stream)
+                                     : launch_half<float>(c, color, (cudaStream_t)stream);
+}
+
+int gadmm_chain_dual_objective(const GadmmChain* c, void* stream) {
+  GADMM_REQUIRE(c && c->Nloc > 0, "chain: every rank must own at least one worker");
+  gadmm_dual_objective_kernel<<<c->Nloc, 256, 0, (cudaStream_t)stream>>>(*c);
+  GADMM_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+int gadmm_chain_iterate(const GadmmChain* c, int n_iter, void* stream) {
+  for (int i = 0; i < n_iter; ++i) {
+    int e;
+    if ((e = gadmm_chain_half_iter(c, 0, stream))) return e;
+    if ((e = gadmm_chain_half_iter(c, 1, stream))) return e;
+    if ((e = gadmm_chain_dual_objective(c, stream))) return e;
+  }
+  return 0;
+}
+
+int gadmm_chain_launches_per_iter(void) { return 3; }
+
+int gadmm_chain_configure(void) {
+  if (int e = configure_half<double>()) return e;
+  return configure_half<float>();
+}
+
+}  // extern "C"

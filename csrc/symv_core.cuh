@@ -1,0 +1,178 @@
+// Packed-symmetric streaming SYMV core (one CTA = two tile-rows of one matrix).
+//
+// Layout: lower block-triangle of 64x64 row-major tiles, tile (I,J) at index I(I+1)/2+J, diagonal
+// tiles stored full.  Reading only the lower triangle halves the HBM bytes of y = S x, which is
+// the whole cost of a GADMM half-iteration (d^2 bytes per worker, memory bound).
+//
+// CTA structure (288 threads): warp 8 is the producer -- it streams tiles global -> shared with
+// cp.async.bulk (UBLKCP) through a STAGES-deep mbarrier ring and assembles the matching 64-entry
+// slice of x (the fused RHS) beside every tile; warps 0..7 are consumers -- warp w owns rows
+// 8w..8w+7 of every tile, lane l owns columns 2l,2l+1.  Per element: one FMA into the row sum
+// (y_I += T x_J) and one into the column sum (y_J += T' x_I), all in fp64, no shuffles in the
+// inner loop.  Row sums are finished inside the CTA; column sums go to `colpart` and are added
+// by the finisher (the last CTA of the matrix, found with an atomic ticket) in a fixed order, so
+// results are bit-reproducible run to run.
+#pragma once
+#include "common.cuh"
+
+namespace gadmm {
+
+constexpr int kT = GADMM_TILE;           // 64
+constexpr int kConsumerWarps = 8;
+constexpr int kSymvThreads = (kConsumerWarps + 1) * 32;  // 288
+constexpr int kRowsPerWarp = kT / kConsumerWarps;        // 8
+
+template <typename T> struct SymvCfg;
+template <> struct SymvCfg<double> { static constexpr int STAGES = 3; };
+template <> struct SymvCfg<float>  { static constexpr int STAGES = 6; };
+
+template <typename T>
+struct SymvSmem {
+  static constexpr int STAGES = SymvCfg<T>::STAGES;
+  alignas(128) T tile[STAGES][kT * kT];
+  alignas(16) double xs[STAGES][kT];          // x_J slice travelling with each tile
+  alignas(16) double xrow[2][kT];             // x_I slices of the CTA's two tile-rows
+  alignas(16) double colbuf[2][kConsumerWarps][kT];
+  alignas(8) uint64_t full[STAGES];
+  alignas(8) uint64_t empty[STAGES];
+  unsigned int ticket;
+};
+
+__host__ __device__ inline size_t colpart_elems(int dp) {
+  const size_t nT = dp / kT;
+  return (size_t)kT * (nT * (nT - 1) / 2);   // sum over tile-rows I of I*64 column partials
+}
+// colpart layout: for tile-row I, J<I: 64 doubles at  (I*(I-1)/2 + J) * 64
+__host__ __device__ inline size_t colpart_off(int I, int J) {
+  return ((size_t)I * (I - 1) / 2 + J) * kT;
+}
+
+__device__ __forceinline__ double2 ld_pair(const double* p) {
+  return *reinterpret_cast<const double2*>(p);
+}
+__device__ __forceinline__ double2 ld_pair(const float* p) {
+  const float2 f = *reinterpret_cast<const float2*>(p);
+  return make_double2((double)f.x, (double)f.y);
+}
+
+// Streams the CTA's tiles and writes rowpart / colpart.  Returns true (to every thread) in the
+// CTA that completed matrix `k` last.  `xf(j)` yields element j of the input vector.
+//   S        packed matrix of this worker
+//   pairIdx  which pair of tile-rows (pairIdx, nT-1-pairIdx) this CTA owns
+template <typename T, typename XF>
+__device__ bool symv_cta(SymvSmem<T>& sm, const T* __restrict__ S, int nT, int pairIdx,
+                         const XF& xf, double* __restrict__ rowpart, double* __restrict__ colpart,
+                         unsigned int* counter, int ctas_per_matrix) {
+  constexpr int STAGES = SymvSmem<T>::STAGES;
+  constexpr uint32_t kTileBytes = kT * kT * sizeof(T);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+
+  if (tid == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&sm.full[s], 1);
+      mbar_init(&sm.empty[s], kConsumerWarps);
+    }
+    mbar_fence_init();
+  }
+  __syncthreads();
+
+  const int rowA = pairIdx, rowB = nT - 1 - pairIdx;
+  const int nrows = (rowA == rowB) ? 1 : 2;
+
+  if (warp == kConsumerWarps) {
+    // ------------------------------------------------------------------ producer warp
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int rr = 0; rr < nrows; ++rr) {
+      const int I = rr == 0 ? rowA : rowB;
+      // x_I slice for the column products of this tile-row
+      sm.xrow[rr][lane] = xf(I * kT + lane);
+      sm.xrow[rr][lane + 32] = xf(I * kT + lane + 32);
+      const T* rowbase = S + ((size_t)I * (I + 1) / 2) * (kT * kT);
+      for (int J = 0; J <= I; ++J) {
+        mbar_wait(&sm.empty[stage], phase ^ 1);
+        if (lane == 0) bulk_g2s(sm.tile[stage], rowbase + (size_t)J * (kT * kT), kTileBytes,
+                                &sm.full[stage]);
+        sm.xs[stage][lane] = xf(J * kT + lane);
+        sm.xs[stage][lane + 32] = xf(J * kT + lane + 32);
+        __syncwarp();
+        if (lane == 0) mbar_arrive_expect_tx(&sm.full[stage], kTileBytes);
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else {
+    // ------------------------------------------------------------------ consumer warps
+    int stage = 0;
+    uint32_t phase = 0;
+    int t = 0;  // running tile counter (colbuf double buffer)
+    for (int rr = 0; rr < nrows; ++rr) {
+      const int I = rr == 0 ? rowA : rowB;
+      double acc_row[kRowsPerWarp];
+      double xr[kRowsPerWarp];
+#pragma unroll
+      for (int r = 0; r < kRowsPerWarp; ++r) acc_row[r] = 0.0;
+      for (int J = 0; J <= I; ++J, ++t) {
+        mbar_wait(&sm.full[stage], phase);
+        if (J == 0) {
+#pragma unroll
+          for (int r = 0; r < kRowsPerWarp; ++r) xr[r] = sm.xrow[rr][warp * kRowsPerWarp + r];
+        }
+        const double2 xj = *reinterpret_cast<const double2*>(&sm.xs[stage][2 * lane]);
+        const T* tp = &sm.tile[stage][(warp * kRowsPerWarp) * kT + 2 * lane];
+        double2 acc_col = make_double2(0.0, 0.0);
+#pragma unroll
+        for (int r = 0; r < kRowsPerWarp; ++r) {
+          const double2 a = ld_pair(tp + r * kT);
+          acc_row[r] = fma(a.x, xj.x, acc_row[r]);
+          acc_row[r] = fma(a.y, xj.y, acc_row[r]);
+          acc_col.x = fma(a.x, xr[r], acc_col.x);
+          acc_col.y = fma(a.y, xr[r], acc_col.y);
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&sm.empty[stage]);
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        if (J < I) {
+          double* cb = sm.colbuf[t & 1][warp];
+          *reinterpret_cast<double2*>(&cb[2 * lane]) = acc_col;
+          asm volatile("bar.sync 1, %0;" ::"n"(kConsumerWarps * 32) : "memory");
+          if (tid < kT) {
+            double s = 0.0;
+#pragma unroll
+            for (int w = 0; w < kConsumerWarps; ++w) s += sm.colbuf[t & 1][w][tid];
+            colpart[colpart_off(I, J) + tid] = s;
+          }
+        }
+      }
+      // finish the row sums of this tile-row inside the warp
+#pragma unroll
+      for (int r = 0; r < kRowsPerWarp; ++r) acc_row[r] = warp_sum(acc_row[r]);
+      if (lane == 0) {
+#pragma unroll
+        for (int r = 0; r < kRowsPerWarp; ++r)
+          rowpart[I * kT + warp * kRowsPerWarp + r] = acc_row[r];
+      }
+    }
+  }
+  // ---- ticket: the last CTA of this matrix becomes the finisher
+  __threadfence();
+  __syncthreads();
+  if (tid == 0) sm.ticket = atomicAdd(counter, 1u);
+  __syncthreads();
+  const bool last = (sm.ticket == (unsigned)(ctas_per_matrix - 1));
+  if (last) {
+    __threadfence();
+    if (tid == 0) *counter = 0u;   // re-arm for the next launch
+  }
+  return last;
+}
+
+// y_j = rowpart[j] + sum_{I > j/64} colpart(I, j/64)[j%64], fixed order (deterministic).
+__device__ __forceinline__ double symv_gather(const double* rowpart, const double* colpart, int nT,
+                                              int j) {
+  const int J = j / kT, jj = j % kT;
+  double v = __ldcg(rowpart + j);
+  for (int I = J + 1; I < nT; ++I) v += __ldcg(colpart + colpart_off(I, J) + jj);
+  return v;
+}
+
+}  // namespace gadmm

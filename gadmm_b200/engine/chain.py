@@ -1,0 +1,340 @@
+"""Chain GADMM / D-GADMM engine: device state, worker->GPU packing, launch loop.
+
+One instance per process (= per GPU).  Logical workers are packed as contiguous id ranges onto
+the ranks (:func:`gadmm_b200.parallel.runtime.partition`); every rank holds
+
+  * the packed inverses ``(G_n + c rho I)^-1`` of its own workers (the d^2 state never moves),
+  * a full replica of the theta table ``[2][N][dp]`` in symmetric memory -- own rows are written
+    by the local finisher CTAs, rows of remote chain neighbours arrive as NVLink P2P stores from
+    the owning GPU's kernel, guarded by per-worker version flags,
+  * node duals, chain tables, per-iteration objective / loss / clock rings.
+
+An iteration is three launches (head half-iteration, tail half-iteration, dual+objective), all
+iteration-agnostic (the iteration counter lives on the device), so a window of iterations is
+captured once in a CUDA graph and replayed.  Reference semantics: group_ADMM_closedForm.m:11-108,
+static_group_ADMM_closedForm.m:19-160, dynamic_group_ADMM_closedForm.m:14-190.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import numpy as np
+import torch
+
+from ..ops import linalg as LA
+from ..ops import native as nv
+from ..parallel.runtime import Dist, partition
+from ..topology import chain_tables
+
+
+def _carve(buf: torch.Tensor, off: int, nbytes: int, dtype) -> torch.Tensor:
+    return buf[off:off + nbytes].view(dtype)
+
+
+class ChainEngine:
+    def __init__(self, N: int, d: int, rho: float, obj0: float, acc: float, max_iter: int,
+                 dist: Optional[Dist] = None, store: str = "f64", dynamic: bool = False,
+                 stop: bool = True):
+        self.dist = dist or Dist()
+        self.dev = self.dist.device
+        self.N, self.d, self.rho = int(N), int(d), float(rho)
+        self.dp = nv.padded(self.d)
+        self.obj0, self.acc, self.max_iter = float(obj0), float(acc), int(max_iter)
+        self.store = nv.STORE_F64 if store in ("f64", "fp64", nv.STORE_F64) else nv.STORE_F32
+        self.dynamic = dynamic
+        self.stop = stop
+        self.owner_np = partition(self.N, self.dist.world)
+        self.gids = np.nonzero(self.owner_np == self.dist.rank)[0].astype(np.int32)
+        self.Nloc = int(self.gids.shape[0])
+        if self.Nloc == 0:
+            raise ValueError("every rank must own at least one worker (N >= world size)")
+        self._alloc()
+        self._graphs = {}
+        self.launches = 0
+        self.path0 = None
+
+    # ------------------------------------------------------------------------------ memory
+    def _alloc(self):
+        N, dp, Nloc, W = self.N, self.dp, self.Nloc, self.dist.world
+        dev = self.dev
+        f64, i32, i64 = torch.float64, torch.int32, torch.int64
+        # symmetric region: theta[2][N][dp] | flags[N] | objpart[4][W] | objflag[4][W]
+        sz_theta = 2 * N * dp * 8
+        sz_flags = (N * 8 + 255) // 256 * 256
+        sz_op = (4 * W * 8 + 255) // 256 * 256
+        self._sym = self.dist.symm_bytes(sz_theta + sz_flags + 2 * sz_op)
+        buf = self._sym.local
+        self.theta = _carve(buf, 0, sz_theta, f64).view(2, N, dp)
+        self.flags = _carve(buf, sz_theta, N * 8, i64)
+        self.objpart = _carve(buf, sz_theta + sz_flags, 4 * W * 8, f64)
+        self.objflag = _carve(buf, sz_theta + sz_flags + sz_op, 4 * W * 8, i64)
+        peers = self._sym.peer_ptrs
+
+        def table(off):
+            return torch.tensor([p + off for p in peers], dtype=i64, device=dev)
+
+        self.theta_peer = table(0)
+        self.flags_peer = table(sz_theta)
+        self.objpart_peer = table(sz_theta + sz_flags)
+        self.objflag_peer = table(sz_theta + sz_flags + sz_op)
+
+        self.b = torch.zeros((Nloc, dp), dtype=f64, device=dev)
+        self.hyy = torch.zeros((Nloc,), dtype=f64, device=dev)
+        self.nu = torch.zeros((Nloc, dp), dtype=f64, device=dev)
+        cpe = max(1, (dp // 64) * (dp // 64 - 1) // 2 * 64)
+        self.rowpart = torch.empty((Nloc, dp), dtype=f64, device=dev)
+        self.colpart = torch.empty((Nloc, cpe), dtype=f64, device=dev)
+        self.counters = torch.zeros((Nloc + 1,), dtype=i32, device=dev)
+        self.objw = torch.zeros((Nloc,), dtype=f64, device=dev)
+        self.ctrl = torch.zeros((4,), dtype=i64, device=dev)
+        self.obj_hist = torch.zeros((self.max_iter + 2,), dtype=f64, device=dev)
+        self.loss_hist = torch.zeros((self.max_iter + 2,), dtype=f64, device=dev)
+        self.t_hist = torch.zeros((self.max_iter + 2,), dtype=i64, device=dev)
+        # chain tables: one int32 block [7][Nloc] so a re-chain is a single H2D copy
+        self.tab = torch.zeros((7, Nloc), dtype=i32, device=dev)
+        self.tab_host = torch.zeros((7, Nloc), dtype=i32).pin_memory()
+        self.tab_host[0] = torch.from_numpy(self.gids)
+        self.owner = torch.from_numpy(self.owner_np).to(dev)
+        self.Mptr = torch.zeros((Nloc,), dtype=i64, device=dev)
+        self.Mptr_host = torch.zeros((Nloc,), dtype=i64).pin_memory()
+        pe = nv.packed_elems(dp)
+        dt = f64 if self.store == nv.STORE_F64 else torch.float32
+        # static chains need one inverse per worker; dynamic chains keep c=1 and c=2 (a worker
+        # becomes / ceases to be a chain end when the chain is re-drawn)
+        self.P = {2: torch.empty((Nloc, pe), dtype=dt, device=dev)}
+        if self.dynamic:
+            self.P[1] = torch.empty((Nloc, pe), dtype=dt, device=dev)
+        else:
+            self.P_end = {}   # local index -> (1, pe) tensor for chain-end workers (c=1)
+        self.ctrl[0] = 1
+        self.ctrl[2] = 1 if self.stop else 0
+
+    # ------------------------------------------------------------------------------- setup
+    def ingest_host(self, XX, YY, s: int, end_workers=(None,), batch: int = 0):
+        """Upload the local workers' shards, build Gram / RHS / inverses on the GPU."""
+        XX = np.asarray(XX, dtype=np.float64)
+        YY = np.asarray(YY, dtype=np.float64).reshape(-1)
+        d, Nloc = self.d, self.Nloc
+        if batch <= 0:
+            per = self.dp * self.dp * 8 * 4 + s * d * 8
+            batch = max(1, min(Nloc, int(8e9 // per)))
+        for k0 in range(0, Nloc, batch):
+            k1 = min(Nloc, k0 + batch)
+            g0, g1 = int(self.gids[k0]), int(self.gids[k1 - 1]) + 1
+            Xb = torch.from_numpy(XX[g0 * s:g1 * s, :d].reshape(g1 - g0, s, d)).to(self.dev)
+            yb = torch.from_numpy(YY[g0 * s:g1 * s].reshape(g1 - g0, s)).to(self.dev)
+            self.ingest_device(Xb, yb, k0)
+
+    def ingest_device(self, Xb: torch.Tensor, yb: torch.Tensor, k0: int):
+        """Xb: (nb, s, d) fp64 on this device for local workers k0..k0+nb."""
+        nb = Xb.shape[0]
+        G, b, hyy = LA.gram(Xb, yb, self.dp)
+        self.ingest_gram(G, b, hyy, k0)
+
+    def ingest_gram(self, G: torch.Tensor, b: torch.Tensor, hyy: torch.Tensor, k0: int):
+        nb = G.shape[0]
+        self.b[k0:k0 + nb] = b
+        self.hyy[k0:k0 + nb] = hyy
+        A = LA.shifted_inverse(G, self.d, 2.0 * self.rho)
+        LA.pack_sym(A, self.d, self.store, out=self.P[2][k0:k0 + nb])
+        if self.dynamic:
+            A = LA.shifted_inverse(G, self.d, 1.0 * self.rho, out=A)
+            LA.pack_sym(A, self.d, self.store, out=self.P[1][k0:k0 + nb])
+        else:
+            self._G_keep = getattr(self, "_G_keep", {})
+            # keep the Gram of potential chain ends (first / last worker id) for the c=1 inverse
+            for g_end in (0, self.N - 1):
+                k = int(np.searchsorted(self.gids, g_end))
+                if k < self.Nloc and self.gids[k] == g_end and k0 <= k < k0 + nb:
+                    self._G_keep[k] = G[k - k0:k - k0 + 1].clone()
+
+    def set_theta(self, theta0):
+        """Optional non-zero start (BASELINE.json: 'random-init theta'); default zeros = reference."""
+        t = torch.as_tensor(np.asarray(theta0, dtype=np.float64).T).to(self.dev)   # (N, d)
+        self.theta[:, :, :self.d] = t.unsqueeze(0)
+
+    # ------------------------------------------------------------------------------ topology
+    def set_path(self, path0, sync_tables: bool = True):
+        """Install a chain (0-based permutation).  Stream-ordered: safe between iterations."""
+        path0 = np.asarray(path0, dtype=np.int64)
+        left, right, color, cmul = chain_tables(path0)
+        g = self.gids
+        own = self.owner_np
+        rank = self.dist.rank
+        push = np.full((2, self.Nloc), -1, dtype=np.int32)
+        for k, gid in enumerate(g):
+            tg = []
+            for nb in (left[gid], right[gid]):
+                if nb >= 0 and own[nb] != rank and own[nb] not in tg:
+                    tg.append(int(own[nb]))
+            for i, r in enumerate(tg):
+                push[i, k] = r
+        th = self.tab_host
+        th[1] = torch.from_numpy(left[g].astype(np.int32))
+        th[2] = torch.from_numpy(right[g].astype(np.int32))
+        th[3] = torch.from_numpy(color[g].astype(np.int32))
+        th[4] = torch.from_numpy(cmul[g].astype(np.int32))
+        th[5] = torch.from_numpy(push[0])
+        th[6] = torch.from_numpy(push[1])
+        pe_bytes = self.P[2].stride(0) * self.P[2].element_size()
+        base2 = self.P[2].data_ptr()
+        mp = self.Mptr_host
+        for k, gid in enumerate(g):
+            c = int(cmul[gid])
+            if c == 2:
+                mp[k] = base2 + k * pe_bytes
+            elif self.dynamic:
+                mp[k] = self.P[1].data_ptr() + k * pe_bytes
+            else:
+                if k not in self.P_end:
+                    A = LA.shifted_inverse(self._G_keep[k], self.d, 1.0 * self.rho)
+                    self.P_end[k] = LA.pack_sym(A, self.d, self.store)
+                mp[k] = self.P_end[k].data_ptr()
+        self.tab.copy_(th, non_blocking=True)
+        self.Mptr.copy_(mp, non_blocking=True)
+        prev = self.path0
+        self.path0 = path0
+        self.left, self.right = left, right
+        if self.dist.world > 1 and prev is not None:
+            self._gather_new_neighbours()
+
+    def _gather_new_neighbours(self):
+        """After a re-chain: pull theta (latest version) of remote neighbours that were not
+        neighbours before.  All ranks are iteration-aligned here (the per-iteration objective
+        exchange bounds the skew), so the owners' rows are final."""
+        torch.cuda.synchronize(self.dev)
+        self.dist.barrier()
+        it = int(self.ctrl[0].item())           # iteration about to run
+        ver = it - 1
+        slot = ver & 1
+        rank = self.dist.rank
+        need = set()
+        for gid in self.gids:
+            for nb in (self.left[gid], self.right[gid]):
+                if nb >= 0 and self.owner_np[nb] != rank:
+                    need.add(int(nb))
+        row_bytes = self.dp * 8
+        for nb in sorted(need):
+            src = self._sym.peer_ptrs[int(self.owner_np[nb])] + (slot * self.N + nb) * row_bytes
+            dst = self.theta[slot, nb]
+            nv_cudart_memcpy(dst.data_ptr(), src, row_bytes)
+            self.flags[nb] = max(int(self.flags[nb].item()), ver)
+        torch.cuda.synchronize(self.dev)
+        self.dist.barrier()
+
+    # ---------------------------------------------------------------------------- descriptor
+    def desc(self) -> nv.GadmmChain:
+        if getattr(self, "_desc", None) is not None:
+            return self._desc
+        c = nv.GadmmChain()
+        t = self.tab
+        for i, name in enumerate(("gid", "left", "right", "color", "cmul", "push0", "push1")):
+            setattr(c, name, t[i].data_ptr())
+        c.Mptr = self.Mptr.data_ptr()
+        c.owner = self.owner.data_ptr()
+        c.b, c.hyy, c.nu = self.b.data_ptr(), self.hyy.data_ptr(), self.nu.data_ptr()
+        c.theta, c.flags = self.theta.data_ptr(), self.flags.data_ptr()
+        c.theta_peer, c.flags_peer = self.theta_peer.data_ptr(), self.flags_peer.data_ptr()
+        c.objpart, c.objflag = self.objpart.data_ptr(), self.objflag.data_ptr()
+        c.objpart_peer, c.objflag_peer = self.objpart_peer.data_ptr(), self.objflag_peer.data_ptr()
+        c.rowpart, c.colpart = self.rowpart.data_ptr(), self.colpart.data_ptr()
+        c.counters, c.objw, c.ctrl = self.counters.data_ptr(), self.objw.data_ptr(), self.ctrl.data_ptr()
+        c.obj_hist, c.loss_hist, c.t_hist = (self.obj_hist.data_ptr(), self.loss_hist.data_ptr(),
+                                             self.t_hist.data_ptr())
+        c.rho, c.obj0, c.acc = self.rho, self.obj0, self.acc
+        c.d, c.dp, c.Nglob, c.Nloc = self.d, self.dp, self.N, self.Nloc
+        c.rank, c.nranks, c.store, c.max_iter = self.dist.rank, self.dist.world, self.store, self.max_iter
+        self._desc = c
+        return c
+
+    # --------------------------------------------------------------------------------- run
+    def iterate(self, n_iter: int, use_graph: bool = True):
+        """Enqueue ``n_iter`` iterations on the current stream (no host sync)."""
+        L = nv.lib()
+        c = self.desc()
+        if not use_graph or n_iter < 4:
+            nv.check(L.gadmm_chain_iterate(C.byref(c), int(n_iter), nv.stream_ptr()))
+        else:
+            g = self._graphs.get(n_iter)
+            if g is None:
+                torch.cuda.synchronize(self.dev)
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g):
+                    nv.check(L.gadmm_chain_iterate(C.byref(c), int(n_iter), nv.stream_ptr()))
+                self._graphs[n_iter] = g    # capture does not execute; replay below does
+            g.replay()
+        self.launches += 3 * int(n_iter)
+
+    def run(self, num_iter: Optional[int] = None, window: int = 32, rechain=None,
+            coherence: Optional[float] = None, use_graph: bool = True) -> int:
+        """Run until the stop test fires or ``num_iter`` iterations are done.  ``rechain(i)``
+        returns the 0-based chain installed before iteration ``i`` when ``i % coherence == 0``
+        (dynamic_group_ADMM_closedForm.m:18-21).  Returns ``Iter``."""
+        num_iter = self.max_iter if num_iter is None else min(int(num_iter), self.max_iter)
+        nv.lib().gadmm_chain_configure()
+        done = 0
+        while done < num_iter:
+            it_next = done + 1
+            if rechain is not None and coherence is not None and it_next > 1 \
+                    and it_next % coherence == 0:
+                self.set_path(rechain(it_next))
+            n = min(window, num_iter - done)
+            if rechain is not None and coherence is not None and coherence < 1e8:
+                tau = int(coherence)
+                nxt = (it_next // tau + 1) * tau      # next re-chain iteration
+                n = max(1, min(n, nxt - it_next))
+            self.iterate(n, use_graph=use_graph)
+            done += n
+            if self.stop:
+                hit = int(self.ctrl[1].item())      # host sync once per window
+                if hit:
+                    return hit
+        return num_iter
+
+    # ----------------------------------------------------------------------------- results
+    def results(self, Iter: int):
+        torch.cuda.synchronize(self.dev)
+        obj = self.obj_hist[1:Iter + 1].cpu().numpy().copy()
+        loss = self.loss_hist[1:Iter + 1].cpu().numpy().copy()
+        t = self.t_hist[1:Iter + 1].to(torch.float64)
+        tv = (t - t[0]) * 1e-9 if Iter > 0 else t
+        if self.dist.world > 1:
+            import torch.distributed as dist
+            dist.all_reduce(tv, op=dist.ReduceOp.MAX)
+        return obj, loss, Iter, tv.cpu().numpy()
+
+    def state(self):
+        """Checkpointable solver state: theta, duals, iteration, path."""
+        torch.cuda.synchronize(self.dev)
+        it = int(self.ctrl[0].item()) - 1
+        slot = it & 1
+        th_loc = self.theta[slot, torch.from_numpy(self.gids).long().to(self.dev), :self.d]
+        return {"theta_local": th_loc.cpu().numpy().T.copy(), "dual_local": self.nu[:, :self.d].cpu().numpy().T.copy(),
+                "gids": self.gids.copy(), "iteration": it,
+                "path": None if self.path0 is None else self.path0 + 1}
+
+
+def nv_cudart_memcpy(dst_ptr: int, src_ptr: int, nbytes: int):
+    """Peer-to-peer cudaMemcpy through the runtime already loaded by torch (UVA handles peers)."""
+    import ctypes
+    rt = _cudart()
+    err = rt.cudaMemcpy(ctypes.c_void_p(dst_ptr), ctypes.c_void_p(src_ptr), ctypes.c_size_t(nbytes),
+                        ctypes.c_int(4))   # cudaMemcpyDefault
+    if err != 0:
+        raise RuntimeError(f"cudaMemcpy (peer gather) failed with {err}")
+
+
+_rt = None
+
+
+def _cudart():
+    global _rt
+    if _rt is None:
+        import ctypes
+        import glob
+        import os
+        cands = glob.glob(os.path.join(os.path.dirname(torch.__file__), "..", "nvidia",
+                                       "cuda_runtime", "lib", "libcudart.so.12"))
+        _rt = ctypes.CDLL(cands[0] if cands else "libcudart.so.12")
+    return _rt

@@ -1,0 +1,133 @@
+"""Reference-signature wrappers over :class:`ChainEngine` (linear closed-form GADMM family)."""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+from ..parallel.runtime import Dist
+from ..topology import findPath2
+from .chain import ChainEngine
+
+
+def _engine(XX, YY, rho, N, d, s, num_iter, obj0, acc, dynamic, store="f64", dist=None,
+            theta0=None):
+    eng = ChainEngine(N, d, rho, obj0, acc, num_iter, dist=dist or Dist(), store=store,
+                      dynamic=dynamic)
+    eng.ingest_host(XX, YY, s)
+    if theta0 is not None:
+        eng.set_theta(theta0)
+    return eng
+
+
+def _energy(cost_of_iter, Iter):
+    c = np.array([cost_of_iter(i) for i in range(1, Iter + 1)], dtype=np.float64)
+    return np.cumsum(c)
+
+
+def gadmm_closed_form(XX, YY, rho, no_workers, num_feature, noSamples, num_iter, obj0, acc,
+                      store="f64", window=32, dist=None, theta0=None, return_engine=False):
+    """``group_ADMM_closedForm`` on the GPU.  Node-dual form internally; the iterates equal the
+    edge-dual ones (nu_n = lambda_n - lambda_{n-1})."""
+    eng = _engine(XX, YY, rho, no_workers, num_feature, noSamples, num_iter, obj0, acc, False,
+                  store, dist, theta0)
+    eng.set_path(np.arange(no_workers))
+    it = eng.run(num_iter, window=window)
+    res = eng.results(it)
+    return res + (eng,) if return_engine else res
+
+
+def static_gadmm(XX, YY, rho, no_workers, num_feature, noSamples, num_iter, obj0, acc,
+                 coherence_Time, pathCost_static_matrix, store="f64", window=32, dist=None,
+                 return_engine=False):
+    costs = np.atleast_2d(np.asarray(pathCost_static_matrix, dtype=np.float64))
+    eng = _engine(XX, YY, rho, no_workers, num_feature, noSamples, num_iter, obj0, acc, False,
+                  store, dist)
+    eng.set_path(np.arange(no_workers))
+    it = eng.run(num_iter, window=window)
+    obj, loss, it, tv = eng.results(it)
+    tau = coherence_Time
+
+    def cost(i):
+        # row index = number of refreshes so far: j in [2, i] with j % tau == 0
+        kk = int(i // tau) - (1 if tau == 1 else 0)
+        return float(costs[min(kk, costs.shape[0] - 1)].sum())
+
+    res = (obj, loss, it, tv, _energy(cost, it))
+    return res + (eng,) if return_engine else res
+
+
+def _dynamic(XX, YY, rho, N, d, s, num_iter, obj0, acc, first_path, first_cost, tau, next_chain,
+             store, window, dist, return_engine):
+    eng = _engine(XX, YY, rho, N, d, s, num_iter, obj0, acc, True, store, dist)
+    eng.set_path(np.asarray(first_path, dtype=np.int64) - 1)
+    cost_at = {1: float(first_cost)}
+    cur = [float(first_cost)]
+
+    def rechain(i):
+        p1, pc = next_chain(i)
+        cur[0] = float(np.sum(pc))
+        cost_at[i] = cur[0]
+        return np.asarray(p1, dtype=np.int64) - 1
+
+    it = eng.run(num_iter, window=window, rechain=rechain, coherence=tau)
+    obj, loss, it, tv = eng.results(it)
+    per = np.empty(it)
+    c = cost_at[1]
+    for i in range(1, it + 1):
+        c = cost_at.get(i, c)
+        per[i - 1] = c
+    res = (obj, loss, it, tv, np.cumsum(per))
+    return res + (eng,) if return_engine else res
+
+
+def dynamic_gadmm(XX, YY, rho, no_workers, num_feature, noSamples, num_iter, obj0, acc, path,
+                  pathCost, coherence_Time, rng=None, rechain=None, store="f64", window=32,
+                  dist=None, return_engine=False):
+    """D-GADMM with live ``findPath2`` re-chaining (dynamic_group_ADMM_closedForm.m:18-21).  Chains
+    are drawn on rank 0 and broadcast so that every GPU installs the same tables."""
+    dist = dist or Dist()
+    g = np.random.default_rng(rng) if not isinstance(rng, np.random.Generator) else rng
+
+    def next_chain(i):
+        if rechain is not None:
+            return rechain(i)
+        out = findPath2(no_workers, g) if dist.rank == 0 else None
+        out = dist.broadcast_object(out)
+        return out[0], out[1]
+
+    return _dynamic(XX, YY, rho, no_workers, num_feature, noSamples, num_iter, obj0, acc, path,
+                    np.sum(pathCost), coherence_Time, next_chain, store, window, dist,
+                    return_engine)
+
+
+def dynamic_gadmm_v0(XX, YY, rho, no_workers, num_feature, noSamples, num_iter, obj0, acc,
+                     path_matrix, pathCost_matrix, coherence_Time, faithful=True, store="f64",
+                     window=32, dist=None, return_engine=False):
+    paths = np.atleast_2d(np.asarray(path_matrix, dtype=np.int64))
+    costs = np.atleast_2d(np.asarray(pathCost_matrix, dtype=np.float64))
+    kk = [0]
+    first_cost = costs[:, 0].sum() if faithful else costs[0].sum()   # quirk 4 (v0.m:18)
+
+    def next_chain(i):
+        kk[0] += 1
+        return paths[kk[0]], costs[kk[0]]
+
+    return _dynamic(XX, YY, rho, no_workers, num_feature, noSamples, num_iter, obj0, acc,
+                    paths[0], first_cost, coherence_Time, next_chain, store, window, dist,
+                    return_engine)
+
+
+def opt_sol_closed_form(XX, YY, return_theta=False):
+    """Global optimum on the GPU in fp64: normal equations on the summed Gram (K12)."""
+    from ..ops import linalg as LA
+    dev = torch.device("cuda", torch.cuda.current_device())
+    X = torch.as_tensor(np.asarray(XX, dtype=np.float64), device=dev)
+    y = torch.as_tensor(np.asarray(YY, dtype=np.float64).reshape(-1), device=dev)
+    d = X.shape[1]
+    G, b, hyy = LA.gram(X.unsqueeze(0), y.unsqueeze(0))
+    A = LA.shifted_inverse(G, d, 0.0)
+    P = LA.pack_sym(A, d)
+    th = LA.BatchedSymv(P, G.shape[1])(b)[0, :d]
+    r = X @ th - y
+    out = 0.5 * float((r @ r).item())
+    return (out, th.cpu().numpy()) if return_theta else out

@@ -1,0 +1,94 @@
+"""ctypes binding of ``libgadmm_b200.so`` (C ABI declared in ``include/gadmm_b200.h``).
+
+The library is loaded lazily and *loudly*: on a machine with a CUDA device a missing or stale
+shared object is an error, never a silent PyTorch fallback.  Tensors are passed as raw device
+pointers; the current torch CUDA stream is used unless a stream is given.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import torch
+
+from .._native import build as _build
+from .._native import lib_path, needs_build
+
+_lib = None
+
+STORE_F64 = 0
+STORE_F32 = 1
+TILE = 64
+
+_vp = C.c_void_p
+
+
+class GadmmChain(C.Structure):
+    """Mirror of ``struct GadmmChain`` (include/gadmm_b200.h)."""
+    _fields_ = [
+        ("gid", _vp), ("left", _vp), ("right", _vp), ("color", _vp), ("cmul", _vp), ("Mptr", _vp),
+        ("push0", _vp), ("push1", _vp), ("owner", _vp), ("b", _vp), ("hyy", _vp), ("nu", _vp),
+        ("theta", _vp), ("flags", _vp), ("theta_peer", _vp), ("flags_peer", _vp),
+        ("objpart", _vp), ("objflag", _vp), ("objpart_peer", _vp), ("objflag_peer", _vp),
+        ("rowpart", _vp), ("colpart", _vp), ("counters", _vp), ("objw", _vp), ("ctrl", _vp),
+        ("obj_hist", _vp), ("loss_hist", _vp), ("t_hist", _vp),
+        ("rho", C.c_double), ("obj0", C.c_double), ("acc", C.c_double),
+        ("d", C.c_int), ("dp", C.c_int), ("Nglob", C.c_int), ("Nloc", C.c_int), ("rank", C.c_int),
+        ("nranks", C.c_int), ("store", C.c_int), ("max_iter", C.c_int),
+    ]
+
+
+def lib():
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = lib_path()
+    if needs_build():
+        if os.environ.get("GADMM_B200_NO_BUILD") == "1" and os.path.exists(path):
+            pass
+        else:
+            _build()
+    _lib = C.CDLL(path, mode=C.RTLD_GLOBAL)
+    _lib.gadmm_last_error.restype = C.c_char_p
+    _lib.gadmm_packed_elems.restype = C.c_size_t
+    _lib.gadmm_packed_elems.argtypes = [C.c_int]
+    _lib.gadmm_symv_scratch_elems.restype = C.c_size_t
+    _lib.gadmm_symv_scratch_elems.argtypes = [C.c_int]
+    return _lib
+
+
+class NativeError(RuntimeError):
+    pass
+
+
+def check(code: int):
+    if code != 0:
+        msg = lib().gadmm_last_error()
+        raise NativeError(f"gadmm_b200 native call failed ({code}): "
+                          f"{msg.decode(errors='replace') if msg else '?'}")
+
+
+def ptr(t):
+    if t is None:
+        return _vp(0)
+    if isinstance(t, int):
+        return _vp(t)
+    assert t.is_cuda and t.is_contiguous(), "native ops need contiguous CUDA tensors"
+    return _vp(t.data_ptr())
+
+
+def stream_ptr(stream=None):
+    s = torch.cuda.current_stream() if stream is None else stream
+    return _vp(s.cuda_stream)
+
+
+def padded(d: int) -> int:
+    return (d + TILE - 1) // TILE * TILE
+
+
+def packed_elems(dp: int) -> int:
+    return int(lib().gadmm_packed_elems(dp))
+
+
+def symv_scratch_elems(dp: int) -> int:
+    return int(lib().gadmm_symv_scratch_elems(dp))

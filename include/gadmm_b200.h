@@ -1,0 +1,111 @@
+/* gadmm_b200 native library -- C ABI (sm_100a).
+ *
+ * Every entry point returns 0 on success, a cudaError_t value (>0) or -1 (bad argument);
+ * gadmm_last_error() returns the message of the calling thread's last failure.  All pointers are
+ * device pointers unless stated otherwise; `stream` is a cudaStream_t passed as void*.
+ * Memory is owned by the caller (PyTorch's caching allocator / symmetric memory in the Python
+ * runtime); the library allocates nothing unless a function says so.
+ *
+ * Parity citations refer to the read-only MATLAB reference (dayoladejo/GADMM).
+ */
+#ifndef GADMM_B200_H
+#define GADMM_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GADMM_TILE_EDGE 64
+#define GADMM_STORE_F64 0
+#define GADMM_STORE_F32 1
+
+const char* gadmm_last_error(void);
+int gadmm_version(void);
+
+/* ---- packed-symmetric tile layout ---------------------------------------------------------
+ * A symmetric dp x dp matrix (dp = 64*nT) is stored as its lower block-triangle of 64x64
+ * row-major tiles, tile (I,J), J<=I, at index I*(I+1)/2+J; diagonal tiles are stored full. */
+size_t gadmm_packed_elems(int dp);
+
+/* ---- setup (K1, K2, K12; group_ADMM_closedForm.m:39-46 `(H'*H + c*rho*I) \ ...`) ---------- */
+/* G[n] = X_n' X_n (dp x dp row-major, zero padded), b[n] = X_n' y_n (dp), hyy[n] = 0.5*y_n'y_n.
+ * X is [N][s][d] row-major fp64, y is [N][s]. */
+int gadmm_gram_f64(const double* X, const double* y, int N, int s, int d, int dp, double* G,
+                   double* b, double* hyy, void* stream);
+/* A[n] = G[n] + shift*I on the leading d x d block, identity on the padded diagonal. */
+int gadmm_shift_copy(const double* G, double* A, int N, int d, int dp, double shift, void* stream);
+/* In-place batched SPD inverse by blocked Cholesky: A (lower block-triangle read) -> A^-1
+ * (lower block-triangle written).  W: workspace N*dp*dp doubles; Dinv: N*nT*64*64 doubles. */
+int gadmm_spd_inverse_f64(double* A, double* W, double* Dinv, int N, int dp, void* stream);
+/* Pack the lower block-triangle of M[n] into tiles (fp64 or fp32), zeroing rows/cols >= d. */
+int gadmm_pack_sym(const double* M, void* packed, int N, int d, int dp, int store, void* stream);
+/* y[n] = S[n] x[n] for packed symmetric S (plain batched SYMV; used by tests, GD/DGD/LAG
+ * gradients G_n theta, eig_extreme).  scratch: N*(dp + dp*dp/128) doubles (see
+ * gadmm_symv_scratch_elems), counters: N uint32 zero-initialised (left zero on return). */
+size_t gadmm_symv_scratch_elems(int dp);
+int gadmm_symv_batched(const void* const* Sptr, const double* x, double* y, int N, int dp,
+                       int store, double* scratch, unsigned int* counters, void* stream);
+
+/* ---- chain GADMM / D-GADMM hot loop (K3, K4, K5) ------------------------------------------
+ * One half-iteration = one launch of the fused kernel: RHS assembly
+ * r = b_n - nu_n + rho*(theta_l + theta_r), theta_n = M_n r by a packed-symmetric SYMV streamed
+ * with cp.async.bulk + mbarrier, per-worker objective, store of theta_n into the local replica
+ * and -- for workers whose neighbours live on other GPUs -- straight into the peers' replicas
+ * over NVLink followed by a release flag.  (group_ADMM_closedForm.m:13-57 head pass, :61-92 tail
+ * pass; node-dual form static_group_ADMM_closedForm.m:50-80.)  The dual kernel applies
+ * nu_n += rho*(theta_n-theta_r) - rho*(theta_l-theta_n) (static_group_ADMM_closedForm.m:130-144),
+ * reduces the objective across GPUs through peer stores, evaluates the stop test
+ * (group_ADMM_closedForm.m:96-108) and advances the device-resident iteration counter. */
+typedef struct GadmmChain {
+  /* per local worker, length Nloc */
+  const int* gid;            /* global worker id */
+  const int* left;           /* global id of chain predecessor, -1 at the chain start */
+  const int* right;          /* global id of chain successor, -1 at the chain end */
+  const int* color;          /* 0 = head group, 1 = tail group */
+  const int* cmul;           /* c_n: 1 at chain ends, 2 inside */
+  const void* const* Mptr;   /* packed (G_n + c_n*rho*I)^-1 to use this iteration */
+  const int* push0;          /* peer rank that must receive theta_n (or -1) */
+  const int* push1;
+  const int* owner;          /* [Nglob] owning rank of every worker */
+  const double* b;           /* [Nloc][dp]  X_n' y_n */
+  const double* hyy;         /* [Nloc]      0.5*y_n'y_n */
+  double* nu;                /* [Nloc][dp]  node duals */
+  double* theta;             /* [2][Nglob][dp] local replica, slot = version & 1 */
+  unsigned long long* flags; /* [Nglob] version of theta_g present in the local replica */
+  double* const* theta_peer; /* [nranks] replica base pointer on every rank (self included) */
+  unsigned long long* const* flags_peer; /* [nranks] */
+  double* objpart;           /* [4][nranks] per-rank objective partials (ring over iterations) */
+  unsigned long long* objflag; /* [4][nranks] */
+  double* const* objpart_peer;            /* [nranks] */
+  unsigned long long* const* objflag_peer; /* [nranks] */
+  double* rowpart;           /* scratch [Nloc][dp] */
+  double* colpart;           /* scratch [Nloc][dp*dp/128] */
+  unsigned int* counters;    /* [Nloc+1] zero-initialised */
+  double* objw;              /* [Nloc] per-worker objective of the current iteration */
+  unsigned long long* ctrl;  /* [4]: ctrl[0]=iteration about to run (1-based), ctrl[1]=Iter at
+                                which loss<acc first held (0 = not yet), ctrl[2]=stop enabled */
+  double* obj_hist;          /* [max_iter+1] objective per iteration (index = iteration) */
+  double* loss_hist;         /* [max_iter+1] */
+  unsigned long long* t_hist; /* [max_iter+1] %globaltimer at the end of each iteration */
+  double rho;
+  double obj0;
+  double acc;
+  int d, dp, Nglob, Nloc, rank, nranks, store, max_iter;
+} GadmmChain;
+
+int gadmm_chain_half_iter(const GadmmChain* c, int color, void* stream);
+int gadmm_chain_dual_objective(const GadmmChain* c, void* stream);
+/* Convenience: n_iter x (head, tail, dual) on `stream` (capturable into a CUDA graph). */
+int gadmm_chain_iterate(const GadmmChain* c, int n_iter, void* stream);
+/* Set the kernels' shared-memory attributes up front (call once before a CUDA-graph capture). */
+int gadmm_chain_configure(void);
+/* Number of kernel launches gadmm_chain_iterate issues per iteration. */
+int gadmm_chain_launches_per_iter(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GADMM_B200_H */

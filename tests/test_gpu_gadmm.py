@@ -1,0 +1,97 @@
+"""Curve parity of the GPU chain engine against the CPU oracle."""
+import numpy as np
+import pytest
+
+import gadmm_b200 as g
+from gadmm_b200 import oracle as O
+
+pytestmark = pytest.mark.gpu
+
+
+def _cmp(a, b, rtol=1e-9):
+    assert a[2] == b[2], (a[2], b[2])
+    np.testing.assert_allclose(a[0], b[0], rtol=rtol, atol=1e-9)
+    np.testing.assert_allclose(a[1], b[1], rtol=1e-5, atol=1e-8)
+
+
+def test_gadmm_closed_form_matches_oracle_small(small_linear):
+    p = small_linear
+    obj0 = O.opt_sol_closedForm(p["XX"], p["YY"])
+    args = (p["XX"], p["YY"], 2.0, p["N"], p["d"], p["s"], 3000, obj0, 1e-4)
+    a = O.group_ADMM_closedForm(*args)
+    b = g.group_ADMM_closedForm(*args, backend="b200")
+    _cmp(a, b)
+    assert b[3].shape == (b[2],) and b[3][0] == 0.0 and np.all(np.diff(b[3]) > 0)
+
+
+@pytest.mark.parametrize("rho", [3.0, 7.0])
+def test_gadmm_reference_shape(ref_linear, rho):
+    p = ref_linear
+    obj0 = O.opt_sol_closedForm(p["XX"], p["YY"])
+    args = (p["XX"], p["YY"], rho, p["N"], p["d"], p["s"], 4000, obj0, 1e-4)
+    a = O.group_ADMM_closedForm(*args)
+    b = g.group_ADMM_closedForm(*args, backend="b200")
+    _cmp(a, b)
+    b3 = g.group_ADMM(*args, backend="b200")
+    assert len(b3) == 3 and b3[2] == a[2]
+
+
+def test_gadmm_odd_and_tiny_chains():
+    rng = np.random.default_rng(5)
+    for N, s, d in ((1, 9, 5), (2, 9, 5), (3, 9, 5), (7, 20, 66)):
+        XX = rng.standard_normal((N * s, d))
+        YY = rng.standard_normal(N * s)
+        obj0 = O.opt_sol_closedForm(XX, YY)
+        args = (XX, YY, 1.5, N, d, s, 60, obj0, 1e-9)
+        _cmp(O.group_ADMM_closedForm(*args), g.group_ADMM_closedForm(*args, backend="b200"))
+
+
+def test_fp32_storage_tracks_oracle(small_linear):
+    p = small_linear
+    obj0 = O.opt_sol_closedForm(p["XX"], p["YY"])
+    args = (p["XX"], p["YY"], 2.0, p["N"], p["d"], p["s"], 3000, obj0, 1e-4)
+    a = O.group_ADMM_closedForm(*args)
+    b = g.group_ADMM_closedForm(*args, backend="b200", store="f32")
+    assert abs(a[2] - b[2]) <= 2
+    n = min(a[2], b[2])
+    np.testing.assert_allclose(a[0][:n], b[0][:n], rtol=1e-5)
+
+
+def test_static_and_dynamic_match_oracle(small_linear):
+    p = small_linear
+    N = p["N"]
+    obj0 = O.opt_sol_closedForm(p["XX"], p["YY"])
+    rng = np.random.default_rng(0)
+    paths, costs = [], []
+    for _ in range(400):
+        pa, co, _ = g.findPath(N, rng=rng)
+        paths.append(pa)
+        costs.append(co)
+    paths, costs = np.array(paths), np.array(costs)
+    base = (p["XX"], p["YY"], 2.0, N, p["d"], p["s"], 300, obj0, 1e-7)
+    a = O.static_group_ADMM_closedForm(*base, 10, costs)
+    b = g.static_group_ADMM_closedForm(*base, 10, costs, backend="b200")
+    _cmp(a, b)
+    np.testing.assert_allclose(a[4], b[4], rtol=1e-12)
+    for tau in (1, 7):
+        a = O.dynamic_group_ADMM_closedForm_v0(*base, paths, costs, tau)
+        b = g.dynamic_group_ADMM_closedForm_v0(*base, paths, costs, tau, backend="b200")
+        _cmp(a, b)
+        np.testing.assert_allclose(a[4], b[4], rtol=1e-12)
+    k = [0, 0]
+
+    def mk(idx):
+        def f(i):
+            k[idx] += 1
+            return paths[k[idx]], costs[k[idx]]
+        return f
+
+    a = O.dynamic_group_ADMM_closedForm(*base, paths[0], costs[0], 5, rechain=mk(0))
+    b = g.dynamic_group_ADMM_closedForm(*base, paths[0], costs[0], 5, rechain=mk(1), backend="b200")
+    _cmp(a, b)
+
+
+def test_opt_sol_on_gpu(small_linear):
+    p = small_linear
+    assert g.opt_sol_closedForm(p["XX"], p["YY"], backend="b200") == pytest.approx(
+        O.opt_sol_closedForm(p["XX"], p["YY"]), rel=1e-9, abs=1e-9)
