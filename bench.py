@@ -1,0 +1,212 @@
+#!/usr/bin/env python
+"""Headline benchmark: GADMM iterations/s on the scaled synthetic linear-regression config of
+BASELINE.json (1024 logical workers x d=4096, strong scaling over 1/2/4/8 GPUs).
+
+A "step" is one full GADMM iteration: head half-iteration, tail half-iteration, dual update,
+all-rank objective reduction and stop test (group_ADMM_closedForm.m:11-108).  The timed region
+is exactly K steps on the device (CUDA events, max over ranks).  Every step streams all packed
+inverses once (N*d^2/2 elements, 68.7 GB at the default config: far larger than the 126 MB L2,
+so no L2 flush is needed between steps).
+
+    python bench.py --gpus 1 --steps 20 --warmup 3
+    python -m torch.distributed.run --nproc-per-node 8 ... bench.py --gpus 8 --steps 20 --warmup 3
+    python bench.py --impl reference      # the MATLAB reference cannot run here -> "unavailable"
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference", "nccl"])
+    ap.add_argument("--workers", type=int, default=1024)
+    ap.add_argument("--d", type=int, default=4096)
+    ap.add_argument("--s", type=int, default=1024)
+    ap.add_argument("--rho", type=float, default=1.0)
+    ap.add_argument("--store", default="f64", choices=["f64", "f32"])
+    ap.add_argument("--e2e-steps", type=int, default=0, help="0 = same as --steps")
+    ap.add_argument("--verbose", action="store_true")
+    return ap.parse_args()
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index=0):
+        self.rows, self.proc, self.idx = [], None, gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms",
+                 "100", "-i", str(self.idx)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL,
+                text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[1]))
+                mx.append(float(r[2]))
+            except Exception:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown",
+                                "sw_power_cap"), r[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def reference_arm(a):
+    # The reference is 26 MATLAB scripts: `pip install /root/reference` fails ("neither setup.py
+    # nor pyproject.toml"), and neither matlab nor octave exists in this image.
+    print(json.dumps({"impl": "reference", "unavailable":
+                      "reference is MATLAB (.m) code: not pip-installable, no matlab/octave "
+                      "binary in the image"}))
+    return 0
+
+
+def main():
+    a = parse()
+    if a.impl == "reference":
+        return reference_arm(a)
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from gadmm_b200.parallel.runtime import Dist, init_process_group
+
+    rank, world, local = init_process_group("nccl")
+    if world != a.gpus and rank == 0:
+        print(f"warning: --gpus {a.gpus} but WORLD_SIZE={world}", file=sys.stderr)
+    torch.cuda.set_device(local)
+    D = Dist()
+    N, d, s = a.workers, a.d, a.s
+    t_setup0 = time.time()
+
+    if a.impl == "nccl":
+        from gadmm_b200.parallel.nccl_baseline import NcclChainGadmm as Engine
+        eng = Engine(N, d, a.rho, 0.0, 1e-4, a.warmup + a.steps + 8, dist=D)
+        from gadmm_b200.parallel.nccl_baseline import build_scaled_linreg
+    else:
+        from gadmm_b200.engine.chain import ChainEngine
+        from gadmm_b200.engine.scaled import build_scaled_linreg
+        es = a.e2e_steps or a.steps
+        eng = ChainEngine(N, d, a.rho, 0.0, 1e-4, a.warmup + a.steps + es + 8, dist=D,
+                          store=a.store, dynamic=False, stop=False)
+    obj0 = build_scaled_linreg(eng, s, seed=0, verbose=a.verbose)
+    eng.set_path(np.arange(N))
+    torch.cuda.synchronize()
+    D.barrier()
+    setup_s = time.time() - t_setup0
+
+    # ---- warm-up (untimed), then exactly K timed steps; device clock, max over ranks
+    eng.iterate(a.warmup, use_graph=False)
+    torch.cuda.synchronize()
+    D.barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+        time.sleep(0.25)
+    D.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    l0 = getattr(eng, "launches", 0)
+    e0.record()
+    eng.iterate(a.steps, use_graph=False)
+    e1.record()
+    torch.cuda.synchronize()
+    D.barrier()
+    launches = getattr(eng, "launches", 0) - l0
+    ms = D.all_reduce_max(e0.elapsed_time(e1))
+    clocks = sampler.stop() if rank == 0 else None
+
+    # ---- end to end through the public streaming API: per step H2D control block from pinned
+    #      memory, 3 kernels, D2H (objective, loss); host wall clock, max over ranks
+    e2e = None
+    if a.impl == "b200":
+        es = a.e2e_steps or a.steps
+        eng.step()
+        D.barrier()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        last = None
+        for _ in range(es):
+            last = eng.step()
+        torch.cuda.synchronize()
+        wall = D.all_reduce_max(time.perf_counter() - t0)
+        e2e = {"value": es / wall, "unit": "iters/s", "ms_per_step": 1e3 * wall / es,
+               "h2d_bytes_per_step": eng.step_h2d_bytes, "d2h_bytes_per_step": eng.step_d2h_bytes,
+               "last_loss": last[1]}
+
+    obj, loss, it, tv = eng.results(a.warmup + a.steps)
+    if rank == 0:
+        elt = 8 if a.store == "f64" else 4
+        nT = eng.dp // 64
+        bytes_per_step = N * (nT * (nT + 1) // 2) * 64 * 64 * elt
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)),
+                                                "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        hbm = peaks.get("hbm_gbs", 6650.0)
+        gbs = bytes_per_step / world / (ms / a.steps * 1e-3) / 1e9
+        out = {
+            "metric": "GADMM iters/s (one iter = head + tail half-iterations + dual update + "
+                      "objective/stop test)",
+            "value": a.steps / (ms * 1e-3), "unit": "iters/s", "n_gpus": world, "steps": a.steps,
+            "warmup": a.warmup, "ms_per_step": ms / a.steps, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "fp64" if a.store == "f64"
+            else "fp32-storage/fp64-accumulate", "data": "synthetic", "impl": a.impl,
+            "config": {"model": "GADMM closed-form linear regression (group_ADMM_closedForm)",
+                       "workers": N, "d": d, "samples_per_worker": s, "rho": a.rho,
+                       "global_batch": N * s, "seq_len": d,
+                       "parallelism": f"chain-segments x{world} (consensus DP)",
+                       "l2": "inputs larger than L2: every step streams all packed inverses "
+                             f"({bytes_per_step / 1e9:.1f} GB total)"},
+            "gpu_launches": launches, "clocks": clocks, "e2e": e2e,
+            "setup_s": setup_s, "obj0": obj0, "loss_first": float(loss[0]),
+            "loss_last": float(loss[-1]),
+            "roofline": {"algorithmic_GB_per_step_per_gpu": bytes_per_step / world / 1e9,
+                         "achieved_GBps_per_gpu": gbs, "hbm_peak_GBps": hbm,
+                         "frac_of_measured" if peaks else "frac_of_fallback": gbs / hbm},
+        }
+        print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

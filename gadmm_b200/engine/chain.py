@@ -292,6 +292,36 @@ class ChainEngine:
                     return hit
         return num_iter
 
+    # ------------------------------------------------------------------- streaming public API
+    def step(self, path0=None):
+        """One GADMM iteration driven from the host, end to end: the step's control block (chain
+        tables + inverse pointer table; a new chain if ``path0`` is given) is copied host->device
+        from pinned memory, the three kernels run, and ``(objective, loss)`` of the iteration is
+        read back device->host.  This is the user-facing online mode (e.g. D-GADMM where an
+        external radio layer supplies the chain every step).  Returns ``(obj, loss)``."""
+        if not hasattr(self, "_step_out"):
+            self._step_out = torch.zeros((2,), dtype=torch.float64).pin_memory()
+            nv.lib().gadmm_chain_configure()
+            self._it_host = int(self.ctrl[0].item())
+        if path0 is not None:
+            self.set_path(path0)
+        else:
+            self.tab.copy_(self.tab_host, non_blocking=True)
+            self.Mptr.copy_(self.Mptr_host, non_blocking=True)
+        self.iterate(1, use_graph=False)
+        it = self._it_host
+        self._step_out[0:1].copy_(self.obj_hist[it:it + 1], non_blocking=True)
+        self._step_out[1:2].copy_(self.loss_hist[it:it + 1], non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        self._it_host += 1
+        return float(self._step_out[0]), float(self._step_out[1])
+
+    @property
+    def step_h2d_bytes(self) -> int:
+        return self.tab_host.numel() * 4 + self.Mptr_host.numel() * 8
+
+    step_d2h_bytes = 16
+
     # ----------------------------------------------------------------------------- results
     def results(self, Iter: int):
         torch.cuda.synchronize(self.dev)
