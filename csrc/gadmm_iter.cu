@@ -294,3 +294,106 @@ int gadmm_chain_configure(void) {
 }
 
 }  // extern "C"
+
+// ============================================================================================
+// Allocation-free batched SYMV.
+//
+// Who this is for: a caller that is not allowed to (or cannot) obtain device memory at the time
+// it needs y = S x.  Two typical cases: (1) a plug-in living inside a host application that took
+// all device memory into its own arena at start-up and forbids cudaMalloc afterwards (the call
+// would fail or break the host's accounting); (2) a latency-critical control loop, where
+// cudaMalloc / cudaFree are unacceptable because they may synchronise the whole device.  Such a
+// caller still owns its inputs and outputs, but has nowhere to put the row/column partial sums
+// and the per-matrix ticket counters that gadmm_symv_batched() expects in `scratch`/`counters`.
+//
+// Here that working memory is a fixed array inside the library image.  It is reserved on every
+// GPU that loads the library, for the life of the process, so it is kept small:
+//   GADMM_NOALLOC_MAX_MATRICES matrices per call, and
+//   N * gadmm_symv_scratch_elems(dp) <= GADMM_NOALLOC_SCRATCH_DOUBLES (1 Mi doubles = 8 MiB).
+// Larger requests are refused with an error message; nothing is allocated as a fallback.
+//
+// Sharing rules: every call on a device uses the same array.  The ticket counters are cleared at
+// the start of each call (on the caller's stream); the partial sums need no clearing because
+// every slot is written before it is read.  Two calls whose kernels can overlap on the GPU
+// (different streams without an ordering between them) race on the array and give wrong
+// results: keep all calls on one stream or order them with events.
+//
+// First use on a device resolves the device address of the array (cudaGetSymbolAddress) and sets
+// the kernels' shared-memory attribute.  That first call does the set-up work, so make it before
+// starting any stream capture on that device.
+// ============================================================================================
+namespace gadmm {
+
+constexpr size_t kNoAllocMaxMatrices = GADMM_NOALLOC_MAX_MATRICES;
+constexpr size_t kNoAllocCounterDoubles = kNoAllocMaxMatrices * sizeof(unsigned int) / sizeof(double);
+constexpr size_t kNoAllocScratchDoubles = GADMM_NOALLOC_SCRATCH_DOUBLES;
+
+// [ counters (kNoAllocMaxMatrices x u32) | rowpart/colpart partial sums ]
+static __device__ __align__(256) double g_noalloc_arena[kNoAllocCounterDoubles + kNoAllocScratchDoubles];
+
+constexpr int kMaxDevices = 64;
+static double* g_noalloc_ptr[kMaxDevices] = {nullptr};   // device address of the arena, per device
+
+// Once per device, with that device current.  In host code `g_noalloc_arena` is only a handle for
+// the runtime -- handing it to a kernel as if it were a pointer would make the kernel touch the
+// wrong memory -- so the real device address is looked up here and cached.
+static int noalloc_setup(int dev, double** out) {
+  if (g_noalloc_ptr[dev] == nullptr) {
+    double* p = nullptr;
+    GADMM_CUDA_OK(cudaGetSymbolAddress((void**)&p, g_noalloc_arena));
+    GADMM_REQUIRE(p != nullptr, "noalloc symv: cudaGetSymbolAddress returned a null address");
+    GADMM_CUDA_OK(cudaFuncSetAttribute(symv_batched_kernel<double>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)sizeof(SymvSmem<double>)));
+    GADMM_CUDA_OK(cudaFuncSetAttribute(symv_batched_kernel<float>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)sizeof(SymvSmem<float>)));
+    g_noalloc_ptr[dev] = p;
+  }
+  *out = g_noalloc_ptr[dev];
+  return 0;
+}
+
+}  // namespace gadmm
+
+extern "C" {
+
+size_t gadmm_symv_noalloc_max_scratch_elems(void) { return kNoAllocScratchDoubles; }
+int gadmm_symv_noalloc_max_matrices(void) { return (int)kNoAllocMaxMatrices; }
+
+int gadmm_symv_batched_noalloc(const void* const* Sptr, const double* x, double* y, int N, int dp,
+                               int store, void* stream) {
+  GADMM_REQUIRE(dp > 0 && dp % kT == 0, "noalloc symv: dp=%d must be a positive multiple of 64", dp);
+  GADMM_REQUIRE(store == GADMM_STORE_F64 || store == GADMM_STORE_F32,
+                "noalloc symv: bad store %d", store);
+  if (N <= 0) return 0;
+  GADMM_REQUIRE((size_t)N <= kNoAllocMaxMatrices,
+                "noalloc symv: N=%d matrices exceeds the built-in limit of %zu per call", N,
+                kNoAllocMaxMatrices);
+  const size_t need = (size_t)N * gadmm_symv_scratch_elems(dp);
+  GADMM_REQUIRE(need <= kNoAllocScratchDoubles,
+                "noalloc symv: N=%d, dp=%d needs %zu doubles of scratch but the built-in arena "
+                "holds %zu; use gadmm_symv_batched with caller-provided scratch instead",
+                N, dp, need, kNoAllocScratchDoubles);
+  int dev = 0;
+  GADMM_CUDA_OK(cudaGetDevice(&dev));
+  GADMM_REQUIRE(dev >= 0 && dev < kMaxDevices, "noalloc symv: device ordinal %d out of range", dev);
+  double* arena = nullptr;
+  if (int e = noalloc_setup(dev, &arena)) return e;
+  cudaStream_t st = (cudaStream_t)stream;
+  unsigned int* counters = reinterpret_cast<unsigned int*>(arena);
+  double* scratch = arena + kNoAllocCounterDoubles;
+  // the arena keeps whatever the previous call (or an aborted one) left: tickets must start at 0
+  GADMM_CUDA_OK(cudaMemsetAsync(counters, 0, (size_t)N * sizeof(unsigned int), st));
+  const int nT = dp / kT, npairs = (nT + 1) / 2;
+  if (store == GADMM_STORE_F64)
+    symv_batched_kernel<double><<<N * npairs, kSymvThreads, (int)sizeof(SymvSmem<double>), st>>>(
+        Sptr, x, y, dp, scratch, counters);
+  else
+    symv_batched_kernel<float><<<N * npairs, kSymvThreads, (int)sizeof(SymvSmem<float>), st>>>(
+        Sptr, x, y, dp, scratch, counters);
+  GADMM_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+}  // extern "C"

@@ -49,6 +49,22 @@ size_t gadmm_symv_scratch_elems(int dp);
 int gadmm_symv_batched(const void* const* Sptr, const double* x, double* y, int N, int dp,
                        int store, double* scratch, unsigned int* counters, void* stream);
 
+/* Same product with no working memory supplied by the caller (no counterpart in the reference;
+ * added for callers that cannot allocate device memory: plug-ins inside an application that owns
+ * the whole device arena, or latency-critical loops that must avoid cudaMalloc/cudaFree).  The
+ * partial sums and ticket counters live in a fixed array inside the library (held on every GPU
+ * that loads it until the process exits).  Limits: N <= GADMM_NOALLOC_MAX_MATRICES and
+ * N*gadmm_symv_scratch_elems(dp) <= GADMM_NOALLOC_SCRATCH_DOUBLES; beyond them the call fails
+ * with a message and allocates nothing.  All calls on a device share the array: calls that can
+ * overlap on the GPU race -- keep them on one stream.  The first call on a device performs the
+ * one-time set-up and should be made before any stream capture. */
+#define GADMM_NOALLOC_MAX_MATRICES 4096
+#define GADMM_NOALLOC_SCRATCH_DOUBLES (1u << 20)
+size_t gadmm_symv_noalloc_max_scratch_elems(void);
+int gadmm_symv_noalloc_max_matrices(void);
+int gadmm_symv_batched_noalloc(const void* const* Sptr, const double* x, double* y, int N, int dp,
+                               int store, void* stream);
+
 /* ---- chain GADMM / D-GADMM hot loop (K3, K4, K5) ------------------------------------------
  * One half-iteration = one launch of the fused kernel: RHS assembly
  * r = b_n - nu_n + rho*(theta_l + theta_r), theta_n = M_n r by a packed-symmetric SYMV streamed
