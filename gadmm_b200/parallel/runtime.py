@@ -77,10 +77,6 @@ class Dist:
             return SymmBuffer(t, [t.data_ptr()])
         import torch.distributed._symmetric_memory as symm_mem
         group = dist.group.WORLD
-        try:
-            symm_mem.enable_symm_mem_for_group(group.group_name)
-        except Exception:
-            pass
         t = symm_mem.empty(nbytes, dtype=torch.uint8, device=self.device)
         try:
             hdl = symm_mem.rendezvous(t, group=group)

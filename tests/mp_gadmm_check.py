@@ -1,0 +1,53 @@
+"""Multi-rank worker launched by tests/test_multigpu.py through torchrun (one rank per GPU)."""
+import os
+import sys
+
+import numpy as np
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+
+def main():
+    import torch
+    import gadmm_b200 as g
+    from gadmm_b200 import oracle as O
+    from gadmm_b200.parallel.runtime import Dist, init_process_group
+
+    init_process_group("nccl")
+    D = Dist()
+    rng = np.random.default_rng(5)
+    N, s, d = 13, 30, 70
+    XX = rng.standard_normal((N * s, d))
+    YY = rng.standard_normal(N * s)
+    obj0 = O.opt_sol_closedForm(XX, YY)
+    base = (XX, YY, 1.5, N, d, s, 400, obj0, 1e-6)
+    a = O.group_ADMM_closedForm(*base)
+    b = g.group_ADMM_closedForm(*base, backend="b200", dist=D)
+    assert a[2] == b[2], (a[2], b[2])
+    np.testing.assert_allclose(a[0], b[0], rtol=1e-9, atol=1e-9)
+    # dynamic chains: neighbours land on arbitrary GPUs, re-chained every 3 iterations
+    prng = np.random.default_rng(0)
+    paths, costs = [], []
+    for _ in range(420):
+        pa, co, _ = g.findPath(N, rng=prng)
+        paths.append(pa)
+        costs.append(co)
+    paths, costs = np.array(paths), np.array(costs)
+    for tau in (1, 3):
+        a = O.dynamic_group_ADMM_closedForm_v0(*base, paths, costs, tau)
+        b = g.dynamic_group_ADMM_closedForm_v0(*base, paths, costs, tau, backend="b200", dist=D)
+        assert a[2] == b[2], (tau, a[2], b[2])
+        np.testing.assert_allclose(a[0], b[0], rtol=1e-9, atol=1e-9)
+        np.testing.assert_allclose(a[4], b[4], rtol=1e-12)
+    # long run on the static chain: flag protocol stress (no stop), windows replayed as graphs
+    c = g.group_ADMM_closedForm(XX, YY, 1.5, N, d, s, 3000, obj0, 0.0, backend="b200", dist=D)
+    r = O.group_ADMM_closedForm(XX, YY, 1.5, N, d, s, 3000, obj0, 0.0)
+    np.testing.assert_allclose(c[0], r[0], rtol=1e-9, atol=1e-9)
+    D.barrier()
+    if D.rank == 0:
+        print(f"MULTIGPU_OK world={D.world}")
+    torch.distributed.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
