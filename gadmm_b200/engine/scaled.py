@@ -26,8 +26,7 @@ def build_scaled_linreg(eng: ChainEngine, s: int, seed: int = 0, noise: float = 
     gen.manual_seed(1234)
     theta_true = torch.randn(d, dtype=torch.float64, device=dev, generator=gen)
     if batch <= 0:
-        per = dp * dp * 8 * 3 + s * d * 8 * 2
-        batch = max(1, min(eng.Nloc, int(16e9 // per)))
+        batch = 16       # fixed: the per-batch generator seed defines the data set
     Gsum = torch.zeros((dp, dp), dtype=torch.float64, device=dev)
     bsum = torch.zeros((dp,), dtype=torch.float64, device=dev)
     hsum = torch.zeros((), dtype=torch.float64, device=dev)

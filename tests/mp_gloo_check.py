@@ -1,0 +1,42 @@
+"""gloo world_size=2 worker for tests/test_gloo.py (BASELINE.json config 1: plumbing, no GPU)."""
+import os
+import sys
+
+import numpy as np
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+
+def run(rank, world, port, q):
+    os.environ.update(RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(rank),
+                      MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    import torch.distributed as dist
+    import gadmm_b200 as g
+    from gadmm_b200 import oracle as O
+    from gadmm_b200.data import linreg_synthetic
+    rng = np.random.default_rng(0)
+    X, y, Hmax, XX, YY = linreg_synthetic(N=24, s=50, growth=1.3, rng=rng, y=rng.standard_normal(50))
+    obj0 = O.opt_sol_closedForm(XX, YY)
+    base = (XX, YY, 5.0, 24, 50, 50, 1000, obj0, 1e-4)
+    a = O.group_ADMM_closedForm(*base)
+    b = g.group_ADMM_closedForm(*base, backend="gloo")
+    assert a[2] == b[2], (a[2], b[2])
+    np.testing.assert_allclose(a[0], b[0], rtol=1e-9)
+    prng = np.random.default_rng(1)
+    paths, costs = [], []
+    for _ in range(300):
+        pa, co, _ = g.findPath(24, rng=prng)
+        paths.append(pa)
+        costs.append(co)
+    a = O.dynamic_group_ADMM_closedForm_v0(*base, np.array(paths), np.array(costs), 10)
+    b = g.dynamic_group_ADMM_closedForm_v0(*base, np.array(paths), np.array(costs), 10, backend="gloo")
+    assert a[2] == b[2]
+    np.testing.assert_allclose(a[0], b[0], rtol=1e-9)
+    np.testing.assert_allclose(a[4], b[4], rtol=1e-12)
+    a = O.standared_ADMM(XX, YY, 1.0, 24, 50, 50, 2000, obj0, 1e-4)
+    b = g.standared_ADMM(XX, YY, 1.0, 24, 50, 50, 2000, obj0, 1e-4, backend="gloo")
+    assert a[2] == b[2]
+    np.testing.assert_allclose(a[0], b[0], rtol=1e-9)
+    dist.barrier()
+    dist.destroy_process_group()
+    q.put((rank, "ok", int(b[2])))
