@@ -9,7 +9,10 @@ __all__ = ["ChainEngine", "gadmm_closed_form", "static_gadmm", "dynamic_gadmm",
 
 def __getattr__(name):
     # late-bound so importing the chain engine does not require every family to be loaded
-    from . import families
+    import importlib
+    if name.startswith("__"):
+        raise AttributeError(name)
+    families = importlib.import_module(__name__ + ".families")
     if hasattr(families, name):
         return getattr(families, name)
     raise AttributeError(name)

@@ -1,1 +1,71 @@
-"""Remaining algorithm families on the GPU (filled in by later modules)."""
+"""Reference-signature GPU entry points for the baseline families and star ADMM."""
+from __future__ import annotations
+
+import numpy as np
+
+from ..ops import native as nv
+from .first_order import FirstOrder
+
+TRIGGERSLOT = 10
+
+
+def _as_rng(rng):
+    return rng if isinstance(rng, np.random.Generator) else np.random.default_rng(rng)
+
+
+def _six(fo: FirstOrder, alpha, Hmax, N, T, obj0, accuracy, rng):
+    thrd = 10.0 / (alpha ** 2 * N ** 2) / TRIGGERSLOT          # GD_DGD_LAG.m:47
+    thrd5 = 1.0 / (alpha ** 2 * N ** 2) / TRIGGERSLOT          # :65
+    nonprob = Hmax / Hmax.sum()
+    uni = np.concatenate([[0.0], _as_rng(rng).random(T), [0.0]])
+    o_dgd = fo.run_dgd(alpha / 100.0, T, obj0)                 # :127
+    ps = fo.run_shared(nv.FO_LAG_PS, alpha, thrd, Hmax, T, obj0, accuracy)
+    wk = fo.run_shared(nv.FO_LAG_WK, alpha, thrd5, Hmax, T, obj0, accuracy)
+    cy = fo.run_shared(nv.FO_IAG_CYCLIC, alpha / N, 0.0, Hmax, T, obj0, accuracy)
+    ra = fo.run_shared(nv.FO_IAG_RANDOM, alpha / N, 0.0, Hmax, T, obj0, accuracy, uni=uni,
+                       cumprob=np.cumsum(nonprob))
+    return o_dgd, ps, wk, cy, ra
+
+
+def gd_dgd_lag(X, y, num_workers, num_feature, Hmax, num_iter, obj0, X_fede, y_fede, num_sample,
+               rng=None, store="f64"):
+    """GPU ``GD_DGD_LAG`` (19 outputs, GD_DGD_LAG.m:1-4)."""
+    N, d, T = int(num_workers), int(num_feature), int(num_iter)
+    fo = FirstOrder(X_fede, y_fede, N, d, num_sample, logistic=False, store=store)
+    Hmax = np.asarray(Hmax, dtype=np.float64).reshape(-1)[:N]
+    alpha = 1.0 / fo.lambda_max()                              # :19,46
+    gd = fo.run_shared(nv.FO_GD, alpha, 0.0, Hmax, T, obj0, None)
+    dgd, ps, wk, cy, ra = _six(fo, alpha, Hmax, N, T, obj0, None, rng)
+    return (gd[0], gd[1], gd[2], dgd[0], dgd[1], dgd[2], ps[0], ps[1], ps[2], ps[3],
+            wk[0], wk[1], wk[2], wk[3], cy[0], cy[1], ra[0], ra[1], alpha)
+
+
+def gd_dgd_lag_logistic(X, y, num_workers, num_feature, Hmax, num_iter, X_fede, y_fede, num_sample,
+                        lam, accuracy, rng=None, naive=True):
+    """GPU ``GD_DGD_LAG_logistic`` (20 outputs; ``obj1`` = GD's last objective, :131-133)."""
+    N, d, T = int(num_workers), int(num_feature), int(num_iter)
+    fo = FirstOrder(X_fede, y_fede, N, d, num_sample, logistic=True, lam=lam)
+    Hmax = np.asarray(Hmax, dtype=np.float64).reshape(-1)[:N]
+    alpha = 1.0 / (0.25 * fo.lambda_max() + lam)               # :24
+    gd = fo.run_shared(nv.FO_GD, alpha, 0.0, Hmax, T, 0.0, None)
+    obj1 = float(gd[0][-1])
+    loss_gd = np.abs(gd[0] - obj1)
+    dgd, ps, wk, cy, ra = _six(fo, alpha, Hmax, N, T, obj1, accuracy, rng)
+    return (gd[0], loss_gd, gd[2], dgd[0], dgd[1], dgd[2], ps[0], ps[1], ps[2], ps[3],
+            wk[0], wk[1], wk[2], wk[3], cy[0], cy[1], ra[0], ra[1], alpha, obj1)
+
+
+def dual_averaging(XX, YY, no_workers, num_feature, noSamples, num_iter, obj0, acc, alpha,
+                   mode="faithful", return_state=False):
+    fo = FirstOrder(XX, YY, no_workers, num_feature, noSamples, logistic=False)
+    obj, loss, it, tv, Theta = fo.run_dualavg(alpha, int(num_iter), obj0, acc, jacobi=(mode == "jacobi"))
+    res = (obj, loss, it, tv)
+    return res + ({"theta": Theta, "iteration": it},) if return_state else res
+
+
+def dual_averaging_logistic(XX, YY, no_workers, num_feature, noSamples, num_iter, obj0, acc, alpha,
+                            eta, mode="faithful", naive=True, return_state=False):
+    fo = FirstOrder(XX, YY, no_workers, num_feature, noSamples, logistic=True, lam=eta)
+    obj, loss, it, tv, Theta = fo.run_dualavg(alpha, int(num_iter), obj0, acc, jacobi=(mode == "jacobi"))
+    res = (obj, loss, it, tv)
+    return res + ({"theta": Theta, "iteration": it},) if return_state else res

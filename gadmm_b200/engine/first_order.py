@@ -1,0 +1,207 @@
+"""GPU engine for the first-order baselines (GD, DGD, LAG-PS, LAG-WK, IAG, dual averaging).
+
+Each iteration is a gradient-provider launch (packed-symmetric SYMV with the ``-b`` / objective
+epilogue for least squares, the fused logistic gradient for logistic regression) followed by one
+fused update kernel; the iteration counter, upload counters and stop flag live on the device, so
+windows of iterations are replayed as CUDA graphs.  Semantics: GD_DGD_LAG.m, GD_DGD_LAG_logistic.m,
+dual_averaging.m, dual_averaging_logisticReg.m (see ``csrc/first_order.cu``).
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+import torch
+
+from ..ops import linalg as LA
+from ..ops import native as nv
+
+
+class FirstOrder:
+    def __init__(self, XX, YY, N, d, s, logistic=False, lam=0.0, device=None, store="f64"):
+        self.dev = device or torch.device("cuda", torch.cuda.current_device())
+        self.N, self.d, self.s, self.logistic, self.lam = int(N), int(d), int(s), logistic, float(lam)
+        self.dp = nv.padded(self.d)
+        XX = np.asarray(XX, dtype=np.float64)[: N * s, :d]
+        YY = np.asarray(YY, dtype=np.float64).reshape(-1)[: N * s]
+        self.X = torch.from_numpy(np.ascontiguousarray(XX.reshape(N, s, d))).to(self.dev)
+        self.y = torch.from_numpy(np.ascontiguousarray(YY.reshape(N, s))).to(self.dev)
+        G, self.b, self.hyy = LA.gram(self.X, self.y, self.dp)
+        self.Gsum = G.sum(0)
+        self.store = nv.STORE_F64 if store in ("f64", nv.STORE_F64) else nv.STORE_F32
+        if not logistic:
+            self.P = LA.pack_sym(G, self.d, self.store)
+            self.ptrs = LA.ptr_table(self.P)
+            self.scratch = torch.empty((N, nv.symv_scratch_elems(self.dp)), dtype=torch.float64,
+                                       device=self.dev)
+            self.cnt = torch.zeros((N,), dtype=torch.int32, device=self.dev)
+        else:
+            self.wbuf = torch.empty((N, s), dtype=torch.float64, device=self.dev)
+        del G
+        self.Y = torch.zeros((N, self.dp), dtype=torch.float64, device=self.dev)
+        self.fw = torch.zeros((N,), dtype=torch.float64, device=self.dev)
+        self.launches = 0
+
+    # ---------------------------------------------------------------------------------------
+    def lambda_max(self, tol: float = 1e-15, max_it: int = 50000) -> float:
+        """Largest eigenvalue of ``X'X = sum_n G_n`` by power iteration on the packed Gram with the
+        streaming SYMV (K11 ``eig_extreme``; GD_DGD_LAG.m:19 ``max(eig(X_fede'*X_fede))``)."""
+        P = LA.pack_sym(self.Gsum.unsqueeze(0), self.d)
+        mv = LA.BatchedSymv(P, self.dp)
+        g = torch.Generator(device=self.dev)
+        g.manual_seed(0)
+        v = torch.zeros((1, self.dp), dtype=torch.float64, device=self.dev)
+        v[0, :self.d] = torch.rand(self.d, dtype=torch.float64, device=self.dev, generator=g) + 0.5
+        v /= v.norm()
+        lam_prev = 0.0
+        w = torch.empty_like(v)
+        for i in range(max_it):
+            mv(v, out=w)
+            if i % 16 == 15:
+                lam = float((v * w).sum().item())       # Rayleigh quotient (host sync every 16)
+                if abs(lam - lam_prev) <= tol * abs(lam):
+                    return lam
+                lam_prev = lam
+            v = w / w.norm()
+        return float((v * mv(v)).sum().item())
+
+    def provider(self, x: torch.Tensor, stride: int):
+        L = nv.lib()
+        if not self.logistic:
+            nv.check(L.gadmm_symv_grad(nv.ptr(self.ptrs), nv.ptr(x), C.c_longlong(stride),
+                                       nv.ptr(self.b), nv.ptr(self.hyy), nv.ptr(self.Y),
+                                       nv.ptr(self.fw), self.N, self.dp, self.store,
+                                       nv.ptr(self.scratch), nv.ptr(self.cnt), nv.stream_ptr()))
+        else:
+            nv.check(L.gadmm_logistic_grad(nv.ptr(self.X), nv.ptr(self.y), nv.ptr(x),
+                                           C.c_longlong(stride), C.c_double(self.lam), self.N,
+                                           self.s, self.d, self.dp, nv.ptr(self.Y), nv.ptr(self.fw),
+                                           nv.ptr(None), nv.ptr(self.wbuf), nv.stream_ptr()))
+        self.launches += 1
+
+    # ---------------------------------------------------------------------------------------
+    def _hist(self, T):
+        f64, i64 = torch.float64, torch.int64
+        return (torch.zeros((T + 2,), dtype=f64, device=self.dev),
+                torch.zeros((T + 2,), dtype=f64, device=self.dev),
+                torch.zeros((T + 2,), dtype=f64, device=self.dev),
+                torch.zeros((T + 2,), dtype=i64, device=self.dev))
+
+    def _drive(self, body, ctrl, T, stop, window):
+        """Replay ``window`` iterations per CUDA graph until T iterations ran or the stop flag is
+        set (host looks at the flag once per window)."""
+        done = 0
+        graph, glen = None, 0
+        while done < T:
+            n = min(window, T - done)
+            if n >= 8:
+                if graph is None or glen != n:
+                    torch.cuda.synchronize(self.dev)
+                    graph = torch.cuda.CUDAGraph()
+                    with torch.cuda.graph(graph):
+                        for _ in range(n):
+                            body()
+                    glen = n
+                graph.replay()
+            else:
+                for _ in range(n):
+                    body()
+            done += n
+            if stop and int(ctrl[1].item()):
+                break
+        torch.cuda.synchronize(self.dev)
+
+    @staticmethod
+    def _time(t_hist, n):
+        t = t_hist[1:n + 1].to(torch.float64)
+        return ((t - t[0]) * 1e-9).cpu().numpy() if n > 0 else np.zeros(0)
+
+    def run_shared(self, kind, step, thr, Hmax, T, obj0, accuracy=None, uni=None, cumprob=None,
+                   window=256):
+        N, dp, dev = self.N, self.dp, self.dev
+        f64 = torch.float64
+        theta = torch.zeros((dp,), dtype=f64, device=dev)
+        ghat = torch.zeros((N, dp), dtype=f64, device=dev)
+        ghat[:, :self.d] = 1.0                                    # grads = ones (GD_DGD_LAG.m:44)
+        that = torch.zeros((N, dp), dtype=f64, device=dev)
+        dnorm = torch.zeros((10,), dtype=f64, device=dev)
+        obj_h, loss_h, comm_h, t_h = self._hist(T)
+        ctrl = torch.tensor([1, 0, 1 if accuracy is not None else 0, 1], dtype=torch.int64, device=dev)
+        cnt = torch.zeros((2,), dtype=torch.int32, device=dev)
+        hm = torch.as_tensor(np.asarray(Hmax, dtype=np.float64), device=dev)
+        un = torch.as_tensor(np.asarray(uni if uni is not None else np.zeros(T + 2)), dtype=f64,
+                             device=dev)
+        cp = torch.as_tensor(np.asarray(cumprob if cumprob is not None else np.ones(N)), dtype=f64,
+                             device=dev)
+        p = nv.GadmmShared()
+        p.theta, p.Y, p.fw, p.ghat, p.theta_hat = (theta.data_ptr(), self.Y.data_ptr(),
+                                                   self.fw.data_ptr(), ghat.data_ptr(), that.data_ptr())
+        p.dnorm, p.Hmax, p.uni, p.cumprob = dnorm.data_ptr(), hm.data_ptr(), un.data_ptr(), cp.data_ptr()
+        p.obj_hist, p.loss_hist, p.comm_hist, p.t_hist = (obj_h.data_ptr(), loss_h.data_ptr(),
+                                                          comm_h.data_ptr(), t_h.data_ptr())
+        p.ctrl, p.counters = ctrl.data_ptr(), cnt.data_ptr()
+        p.step, p.thr, p.obj0 = float(step), float(thr), float(obj0)
+        p.acc = float(accuracy) if accuracy is not None else 0.0
+        p.N, p.d, p.dp, p.kind, p.max_iter, p.logistic = N, self.d, dp, kind, T, int(self.logistic)
+        L = nv.lib()
+
+        def body():
+            self.provider(theta, 0)
+            nv.check(L.gadmm_shared_update(C.byref(p), nv.stream_ptr()))
+            self.launches += 1
+
+        self._drive(body, ctrl, T, accuracy is not None, window)
+        hit = int(ctrl[1].item())
+        n = hit if hit else T
+        keep = (theta, ghat, that, dnorm, hm, un, cp, cnt)   # alive until here
+        del keep
+        return (obj_h[1:n + 1].cpu().numpy(), loss_h[1:n + 1].cpu().numpy(), self._time(t_h, n),
+                comm_h[1:n + 1].cpu().numpy(), theta[:self.d].cpu().numpy())
+
+    def _own(self, step, T, obj0, acc, stop, jacobi=0):
+        N, dp, dev = self.N, self.dp, self.dev
+        f64 = torch.float64
+        Theta = torch.zeros((N, dp), dtype=f64, device=dev)
+        Z = torch.zeros((N, dp), dtype=f64, device=dev)
+        obj_h, loss_h, _, t_h = self._hist(T)
+        ctrl = torch.tensor([1, 0, 1 if stop else 0, 0], dtype=torch.int64, device=dev)
+        cnt = torch.zeros((1,), dtype=torch.int32, device=dev)
+        p = nv.GadmmOwn()
+        p.Theta, p.Y, p.fw, p.Z = Theta.data_ptr(), self.Y.data_ptr(), self.fw.data_ptr(), Z.data_ptr()
+        p.obj_hist, p.loss_hist, p.t_hist = obj_h.data_ptr(), loss_h.data_ptr(), t_h.data_ptr()
+        p.ctrl, p.counters = ctrl.data_ptr(), cnt.data_ptr()
+        p.step, p.obj0, p.acc = float(step), float(obj0), float(acc)
+        p.N, p.d, p.dp, p.max_iter, p.jacobi = N, self.d, dp, T, int(jacobi)
+        return p, Theta, Z, obj_h, loss_h, t_h, ctrl, cnt
+
+    def run_dgd(self, step, T, obj0, window=256):
+        p, Theta, Z, obj_h, loss_h, t_h, ctrl, cnt = self._own(step, T, obj0, 0.0, False)
+        L = nv.lib()
+
+        def body():
+            self.provider(Theta, self.dp)
+            nv.check(L.gadmm_dgd_update(C.byref(p), nv.stream_ptr()))
+            self.launches += 1
+
+        self._drive(body, ctrl, T, False, window)
+        return obj_h[1:T + 1].cpu().numpy(), loss_h[1:T + 1].cpu().numpy(), self._time(t_h, T)
+
+    def run_dualavg(self, alpha, T, obj0, acc, jacobi=False, window=256):
+        p, Theta, Z, obj_h, loss_h, t_h, ctrl, cnt = self._own(alpha, T, obj0, acc, True, jacobi)
+        L = nv.lib()
+
+        def body():
+            self.provider(Theta, self.dp)
+            nv.check(L.gadmm_dualavg_update(C.byref(p), 1, nv.stream_ptr()))
+            self.launches += 1
+
+        self._drive(body, ctrl, T, True, window)
+        if not int(ctrl[1].item()):
+            # close the last iteration: objective of the final iterate
+            self.provider(Theta, self.dp)
+            nv.check(L.gadmm_dualavg_update(C.byref(p), 0, nv.stream_ptr()))
+            torch.cuda.synchronize(self.dev)
+        hit = int(ctrl[1].item())
+        n = hit if hit else T
+        return (obj_h[1:n + 1].cpu().numpy(), loss_h[1:n + 1].cpu().numpy(), n, self._time(t_h, n),
+                Theta[:, :self.d].cpu().numpy().T)

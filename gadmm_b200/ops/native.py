@@ -92,3 +92,28 @@ def packed_elems(dp: int) -> int:
 
 def symv_scratch_elems(dp: int) -> int:
     return int(lib().gadmm_symv_scratch_elems(dp))
+
+
+class GadmmShared(C.Structure):
+    """Mirror of ``struct GadmmShared`` (include/gadmm_b200.h)."""
+    _fields_ = [
+        ("theta", _vp), ("Y", _vp), ("fw", _vp), ("ghat", _vp), ("theta_hat", _vp), ("dnorm", _vp),
+        ("Hmax", _vp), ("uni", _vp), ("cumprob", _vp), ("obj_hist", _vp), ("loss_hist", _vp),
+        ("comm_hist", _vp), ("t_hist", _vp), ("ctrl", _vp), ("counters", _vp),
+        ("step", C.c_double), ("thr", C.c_double), ("obj0", C.c_double), ("acc", C.c_double),
+        ("N", C.c_int), ("d", C.c_int), ("dp", C.c_int), ("kind", C.c_int), ("max_iter", C.c_int),
+        ("logistic", C.c_int),
+    ]
+
+
+class GadmmOwn(C.Structure):
+    """Mirror of ``struct GadmmOwn`` (include/gadmm_b200.h)."""
+    _fields_ = [
+        ("Theta", _vp), ("Y", _vp), ("fw", _vp), ("Z", _vp), ("obj_hist", _vp), ("loss_hist", _vp),
+        ("t_hist", _vp), ("ctrl", _vp), ("counters", _vp),
+        ("step", C.c_double), ("obj0", C.c_double), ("acc", C.c_double),
+        ("N", C.c_int), ("d", C.c_int), ("dp", C.c_int), ("max_iter", C.c_int), ("jacobi", C.c_int),
+    ]
+
+
+FO_GD, FO_LAG_PS, FO_LAG_WK, FO_IAG_CYCLIC, FO_IAG_RANDOM = range(5)

@@ -121,6 +121,63 @@ int gadmm_chain_configure(void);
 /* Number of kernel launches gadmm_chain_iterate issues per iteration. */
 int gadmm_chain_launches_per_iter(void);
 
+/* ---- first-order baselines (K7, K8; GD_DGD_LAG.m, GD_DGD_LAG_logistic.m, dual_averaging*.m) ---- */
+/* Gradient providers.  Linear: Y[n] = S_n x_n - b_n, fw[n] = 0.5 x'S x - b'x + hyy[n]; x_stride
+ * = 0 shares one iterate between all workers (parameter-server methods). */
+int gadmm_symv_grad(const void* const* Sptr, const double* x, long long x_stride, const double* b,
+                    const double* hyy, double* Y, double* fw, int N, int dp, int store,
+                    double* scratch, unsigned int* counters, void* stream);
+/* Logistic: Y[n] = -X_n'(y./(1+exp(y.*X_n th))) + lam*th, fw[n] = lam/2||th||^2 + sum log(1+exp(-y.*z)),
+ * wout (optional) = sigma(1-sigma) per sample; wbuf: N*s doubles of scratch. */
+int gadmm_logistic_grad(const double* X, const double* y, const double* th, long long th_stride,
+                        double lam, int N, int s, int d, int dp, double* Y, double* fw,
+                        double* wout, double* wbuf, void* stream);
+
+#define GADMM_FO_GD 0
+#define GADMM_FO_LAG_PS 1
+#define GADMM_FO_LAG_WK 2
+#define GADMM_FO_IAG_CYCLIC 3
+#define GADMM_FO_IAG_RANDOM 4
+
+typedef struct GadmmShared {      /* shared-iterate methods: GD, LAG-PS, LAG-WK, IAG */
+  double* theta;                  /* [dp] */
+  const double* Y;                /* [N][dp] fresh gradients at theta */
+  const double* fw;               /* [N] per-worker objective at theta */
+  double* ghat;                   /* [N][dp] server-side (possibly stale) gradients, init ones */
+  double* theta_hat;              /* [N][dp] iterate of each worker's last upload (LAG-PS) */
+  double* dnorm;                  /* [10] ring of ||theta^{k+1}-theta^k||^2 */
+  const double* Hmax;             /* [N] */
+  const double* uni;              /* [max_iter+2] uniforms for R-IAG (index = iteration) */
+  const double* cumprob;          /* [N] cumulative sampling probabilities */
+  double* obj_hist;               /* [max_iter+2] */
+  double* loss_hist;
+  double* comm_hist;              /* comm_iter_final */
+  unsigned long long* t_hist;
+  unsigned long long* ctrl;       /* [0]=iteration (1-based), [1]=hit, [2]=stop enabled, [3]=comm_iter */
+  unsigned int* counters;         /* [2] ticket, upload flag (zero-initialised) */
+  double step, thr, obj0, acc;
+  int N, d, dp, kind, max_iter, logistic;
+} GadmmShared;
+int gadmm_shared_update(const GadmmShared* p, void* stream);
+
+typedef struct GadmmOwn {         /* one iterate per worker: DGD, dual averaging */
+  double* Theta;                  /* [N][dp] */
+  const double* Y;                /* [N][dp] fresh gradients at Theta */
+  const double* fw;               /* [N] */
+  double* Z;                      /* [N][dp] dual-averaging accumulators (Z_prev) */
+  double* obj_hist;
+  double* loss_hist;
+  unsigned long long* t_hist;
+  unsigned long long* ctrl;       /* [0]=iteration, [1]=hit, [2]=stop enabled */
+  unsigned int* counters;         /* [1] */
+  double step, obj0, acc;
+  int N, d, dp, max_iter, jacobi;
+} GadmmOwn;
+int gadmm_dgd_update(const GadmmOwn* p, void* stream);
+/* update=1: record the objective of the previous iterate (from fw), stop test, then one dual
+ * averaging sweep; update=0: record only (closes the last iteration). */
+int gadmm_dualavg_update(const GadmmOwn* p, int update, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
