@@ -1,0 +1,185 @@
+// Standard (star / parameter-server) ADMM, closed form -- K6 of SURVEY.md section 2.4.
+//
+//   workers n < N:  theta_n <- (G_n + rho I)^-1 (b_n - lambda_n + rho z)          standared_ADMM.m:42
+//   server  N    :  z <- (G_N + (N-1) rho I)^-1 (b_N + sum lambda_n + rho sum theta_n)   :66-73
+//   duals        :  lambda_n += rho (theta_n - z)                                          :84-88
+//
+// star_workers_kernel: streamed packed-symmetric SYMV per worker; the dual update of the previous
+// iteration is folded into the RHS assembly (r = b - [lambda + rho(theta - z)] + rho z) and made
+// permanent by the worker's finisher CTA; the globally last finisher reduces
+// u = sum_n (lambda_n + rho theta_n) in a fixed order and pushes it -- together with this GPU's
+// objective partial -- into every GPU's `ubuf` with NVLink P2P stores + st.release.sys.
+// star_server_kernel: replicated on every GPU (no broadcast of z): waits for all ranks' partials
+// with ld.acquire.sys, solves for z, adds the server shard's objective, runs the stop test.
+#include "../include/gadmm_b200.h"
+#include "symv_core.cuh"
+
+namespace gadmm {
+
+constexpr int kUPad = 64;   // ubuf row = dp + kUPad doubles; [dp] carries the objective partial
+
+struct StarWorkerX {
+  const double* b;
+  const double* lam;
+  const double* th;
+  const double* z;
+  double rho;
+  __device__ __forceinline__ double lam_new(int j) const {
+    return lam[j] + rho * (th[j] - z[j]);
+  }
+  __device__ __forceinline__ double operator()(int j) const {
+    return b[j] - lam_new(j) + rho * z[j];
+  }
+};
+
+template <typename T>
+__global__ void __launch_bounds__(kSymvThreads, 2)
+star_workers_kernel(const GadmmStar p) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  SymvSmem<T>& sm = *reinterpret_cast<SymvSmem<T>*>(smem_raw);
+  __shared__ unsigned int gticket;
+  const unsigned long long it = p.ctrl[0];
+  if (p.ctrl[2] != 0ull && p.ctrl[1] != 0ull) return;
+  if (it > (unsigned long long)p.max_iter) return;
+  const int dp = p.dp, nT = dp / kT, npairs = (nT + 1) / 2;
+  const int k = blockIdx.x / npairs, pr = blockIdx.x % npairs;
+  StarWorkerX xf{p.b + (size_t)k * dp, p.lam + (size_t)k * dp, p.theta + (size_t)k * dp, p.z, p.rho};
+  double* rowpart = p.rowpart + (size_t)k * dp;
+  double* colpart = p.colpart + (size_t)k * colpart_elems(dp);
+  const bool last = symv_cta<T>(sm, reinterpret_cast<const T*>(p.Mptr[k]), nT, pr, xf, rowpart,
+                                colpart, p.counters + k, npairs);
+  if (!last) return;
+  // ---- finisher of worker k
+  double* lam = p.lam + (size_t)k * dp;
+  double* th = p.theta + (size_t)k * dp;
+  double* U = p.U + (size_t)k * dp;
+  double s1 = 0.0, s2 = 0.0;
+  for (int j = threadIdx.x; j < dp; j += blockDim.x) {
+    const double ln = xf.lam_new(j);
+    const double r = xf.b[j] - ln + p.rho * p.z[j];
+    const double tn = symv_gather(rowpart, colpart, nT, j);
+    lam[j] = ln;
+    th[j] = tn;
+    U[j] = ln + p.rho * tn;
+    s1 = fma(tn, r - p.rho * tn, s1);
+    s2 = fma(xf.b[j], tn, s2);
+  }
+  double* red = &sm.colbuf[0][0][0];
+  s1 = block_sum(s1, red);
+  s2 = block_sum(s2, red);
+  if (threadIdx.x == 0) p.fw[k] = 0.5 * s1 - s2 + p.hyy[k];
+  // ---- global ticket: the last finisher reduces u and publishes it to every GPU
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) gticket = atomicAdd(p.counters + p.Nw, 1u);
+  __syncthreads();
+  if (gticket != (unsigned)(p.Nw - 1)) return;
+  __threadfence();
+  const size_t row = (size_t)dp + kUPad;
+  const size_t slot = ((size_t)(it & 1ull) * p.nranks + p.rank) * row;
+  double fpart = 0.0;
+  for (int i = threadIdx.x; i < p.Nw; i += blockDim.x) fpart += __ldcg(p.fw + i);
+  fpart = block_sum(fpart, red);
+  for (int j = threadIdx.x; j < dp; j += blockDim.x) {
+    double u = 0.0;
+    for (int i = 0; i < p.Nw; ++i) u += __ldcg(p.U + (size_t)i * dp + j);
+    for (int q = 0; q < p.nranks; ++q) p.ubuf_peer[q][slot + j] = u;
+  }
+  if (threadIdx.x == 0)
+    for (int q = 0; q < p.nranks; ++q) p.ubuf_peer[q][slot + dp] = fpart;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    p.counters[p.Nw] = 0u;
+    __threadfence_system();
+    for (int q = 0; q < p.nranks; ++q)
+      st_release_sys(p.uflag_peer[q] + (it & 1ull) * p.nranks + p.rank, it);
+  }
+}
+
+struct StarServerX {
+  const double* bs;
+  const double* ubuf;   // this iteration's slot base: [nranks][dp + kUPad]
+  int nranks;
+  size_t row;
+  __device__ __forceinline__ double operator()(int j) const {
+    double u = 0.0;
+    for (int q = 0; q < nranks; ++q) u += __ldcg(ubuf + q * row + j);   // fixed rank order
+    return bs[j] + u;
+  }
+};
+
+template <typename T>
+__global__ void __launch_bounds__(kSymvThreads, 2)
+star_server_kernel(const GadmmStar p) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  SymvSmem<T>& sm = *reinterpret_cast<SymvSmem<T>*>(smem_raw);
+  const unsigned long long it = p.ctrl[0];
+  if (p.ctrl[2] != 0ull && p.ctrl[1] != 0ull) return;
+  if (it > (unsigned long long)p.max_iter) return;
+  const int dp = p.dp, nT = dp / kT, npairs = (nT + 1) / 2;
+  if (threadIdx.x == kConsumerWarps * 32)
+    for (int q = 0; q < p.nranks; ++q) wait_flag_ge(p.uflag + (it & 1ull) * p.nranks + q, it);
+  __syncthreads();
+  const size_t row = (size_t)dp + kUPad;
+  const double* ub = p.ubuf + (size_t)(it & 1ull) * p.nranks * row;
+  StarServerX xf{p.bs, ub, p.nranks, row};
+  double* rowpart = p.rowpart + (size_t)p.Nw * dp;
+  double* colpart = p.colpart + (size_t)p.Nw * colpart_elems(dp);
+  const bool last = symv_cta<T>(sm, reinterpret_cast<const T*>(p.Ms), nT, blockIdx.x, xf, rowpart,
+                                colpart, p.counters + p.Nw + 1, npairs);
+  if (!last) return;
+  const double crho = p.rho * (double)(p.N - 1);
+  double s1 = 0.0, s2 = 0.0;
+  for (int j = threadIdx.x; j < dp; j += blockDim.x) {
+    const double zn = symv_gather(rowpart, colpart, nT, j);
+    const double r = xf(j);
+    p.z[j] = zn;
+    s1 = fma(zn, r - crho * zn, s1);
+    s2 = fma(p.bs[j], zn, s2);
+  }
+  double* red = &sm.colbuf[0][0][0];
+  s1 = block_sum(s1, red);
+  s2 = block_sum(s2, red);
+  if (threadIdx.x == 0) {
+    double total = 0.5 * s1 - s2 + p.hyy_s;
+    for (int q = 0; q < p.nranks; ++q) total += __ldcg(ub + q * row + dp);
+    const double loss = fabs(total - p.obj0);
+    p.obj_hist[it] = total;
+    p.loss_hist[it] = loss;
+    p.t_hist[it] = globaltimer_ns();
+    if (loss < p.acc && p.ctrl[1] == 0ull) p.ctrl[1] = it;
+    p.ctrl[0] = it + 1ull;
+  }
+}
+
+template <typename T>
+static int star_iterate(const GadmmStar* p, int n_iter, cudaStream_t st) {
+  const int smem = (int)sizeof(SymvSmem<T>);
+  static bool configured = false;
+  if (!configured) {
+    GADMM_CUDA_OK(cudaFuncSetAttribute(star_workers_kernel<T>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    GADMM_CUDA_OK(cudaFuncSetAttribute(star_server_kernel<T>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    configured = true;
+  }
+  const int nT = p->dp / kT, npairs = (nT + 1) / 2;
+  for (int i = 0; i < n_iter; ++i) {
+    star_workers_kernel<T><<<p->Nw * npairs, kSymvThreads, smem, st>>>(*p);
+    star_server_kernel<T><<<npairs, kSymvThreads, smem, st>>>(*p);
+  }
+  GADMM_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace gadmm
+
+using namespace gadmm;
+
+extern "C" int gadmm_star_iterate(const GadmmStar* p, int n_iter, void* stream) {
+  GADMM_REQUIRE(p && p->dp > 0 && p->dp % kT == 0, "star: dp must be a positive multiple of 64");
+  GADMM_REQUIRE(p->Nw > 0, "star: every rank must own at least one worker");
+  if (p->store == GADMM_STORE_F64) return star_iterate<double>(p, n_iter, (cudaStream_t)stream);
+  if (p->store == GADMM_STORE_F32) return star_iterate<float>(p, n_iter, (cudaStream_t)stream);
+  return set_error(-1, "star: bad store %d", p->store);
+}

@@ -1,0 +1,137 @@
+"""Star (parameter-server) ADMM engine -- ``standared_ADMM`` on the GPU (K6).
+
+The N-1 workers are split into contiguous id ranges over the ranks; the server shard (worker N)
+is replicated on every rank so that the z-solve needs no broadcast.  Per iteration: one workers
+kernel (solves + fused dual update + in-kernel reduction pushed to all GPUs over NVLink) and one
+server kernel.  See ``csrc/star.cu``.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+import torch
+
+from ..ops import linalg as LA
+from ..ops import native as nv
+from ..parallel.runtime import Dist, partition
+
+
+class StarEngine:
+    def __init__(self, XX, YY, rho, N, d, s, max_iter, obj0, acc, dist=None, store="f64", stop=True):
+        self.dist = dist or Dist()
+        D = self.dist
+        dev = self.dev = D.device
+        self.N, self.d, self.dp, self.rho = int(N), int(d), nv.padded(int(d)), float(rho)
+        self.store = nv.STORE_F64 if store in ("f64", nv.STORE_F64) else nv.STORE_F32
+        self.max_iter = int(max_iter)
+        if N < 2:
+            raise ValueError("star ADMM needs at least one worker besides the server")
+        owner = partition(N - 1, D.world)
+        self.gids = np.nonzero(owner == D.rank)[0]
+        Nw = self.Nw = len(self.gids)
+        if Nw == 0:
+            raise ValueError("every rank must own at least one worker")
+        XX = np.asarray(XX, dtype=np.float64)
+        YY = np.asarray(YY, dtype=np.float64).reshape(-1)
+        dp, f64 = self.dp, torch.float64
+        g0, g1 = int(self.gids[0]), int(self.gids[-1]) + 1
+        X = torch.from_numpy(XX[g0 * s:g1 * s, :d].reshape(Nw, s, d)).to(dev)
+        y = torch.from_numpy(YY[g0 * s:g1 * s].reshape(Nw, s)).to(dev)
+        G, self.b, self.hyy = LA.gram(X, y, dp)
+        self.P = LA.pack_sym(LA.shifted_inverse(G, d, rho), d, self.store)
+        self.Mptr = LA.ptr_table(self.P)
+        Xs = torch.from_numpy(XX[(N - 1) * s:N * s, :d].reshape(1, s, d)).to(dev)
+        ys = torch.from_numpy(YY[(N - 1) * s:N * s].reshape(1, s)).to(dev)
+        Gs, bs, hs = LA.gram(Xs, ys, dp)
+        self.Ps = LA.pack_sym(LA.shifted_inverse(Gs, d, (N - 1) * rho), d, self.store)
+        self.bs, self.hyy_s = bs[0].contiguous(), float(hs[0].item())
+        self.lam = torch.zeros((Nw, dp), dtype=f64, device=dev)
+        self.theta = torch.zeros((Nw, dp), dtype=f64, device=dev)
+        self.z = torch.zeros((dp,), dtype=f64, device=dev)
+        self.U = torch.zeros((Nw, dp), dtype=f64, device=dev)
+        self.fw = torch.zeros((Nw,), dtype=f64, device=dev)
+        W = D.world
+        row = dp + 64
+        sz_u = 2 * W * row * 8
+        self._sym = D.symm_bytes(sz_u + 2 * W * 8)
+        self.ubuf = self._sym.local[:sz_u].view(f64)
+        self.uflag = self._sym.local[sz_u:sz_u + 2 * W * 8].view(torch.int64)
+        self.ubuf_peer = torch.tensor(self._sym.peer_ptrs, dtype=torch.int64, device=dev)
+        self.uflag_peer = torch.tensor([q + sz_u for q in self._sym.peer_ptrs], dtype=torch.int64,
+                                       device=dev)
+        cpe = max(1, (dp // 64) * (dp // 64 - 1) // 2 * 64)
+        self.rowpart = torch.empty((Nw + 1, dp), dtype=f64, device=dev)
+        self.colpart = torch.empty((Nw + 1, cpe), dtype=f64, device=dev)
+        self.counters = torch.zeros((Nw + 2,), dtype=torch.int32, device=dev)
+        self.ctrl = torch.tensor([1, 0, 1 if stop else 0, 0], dtype=torch.int64, device=dev)
+        self.obj_hist = torch.zeros((self.max_iter + 2,), dtype=f64, device=dev)
+        self.loss_hist = torch.zeros((self.max_iter + 2,), dtype=f64, device=dev)
+        self.t_hist = torch.zeros((self.max_iter + 2,), dtype=torch.int64, device=dev)
+        p = self.p = nv.GadmmStar()
+        p.Mptr, p.Ms, p.b, p.hyy, p.bs = (self.Mptr.data_ptr(), self.Ps.data_ptr(), self.b.data_ptr(),
+                                          self.hyy.data_ptr(), self.bs.data_ptr())
+        p.lam, p.theta, p.z, p.U, p.fw = (self.lam.data_ptr(), self.theta.data_ptr(), self.z.data_ptr(),
+                                          self.U.data_ptr(), self.fw.data_ptr())
+        p.ubuf, p.uflag = self.ubuf.data_ptr(), self.uflag.data_ptr()
+        p.ubuf_peer, p.uflag_peer = self.ubuf_peer.data_ptr(), self.uflag_peer.data_ptr()
+        p.rowpart, p.colpart, p.counters = (self.rowpart.data_ptr(), self.colpart.data_ptr(),
+                                            self.counters.data_ptr())
+        p.ctrl, p.obj_hist, p.loss_hist, p.t_hist = (self.ctrl.data_ptr(), self.obj_hist.data_ptr(),
+                                                     self.loss_hist.data_ptr(), self.t_hist.data_ptr())
+        p.rho, p.obj0, p.acc, p.hyy_s = self.rho, float(obj0), float(acc), self.hyy_s
+        p.d, p.dp, p.N, p.Nw, p.rank, p.nranks = self.d, dp, self.N, Nw, D.rank, D.world
+        p.store, p.max_iter = self.store, self.max_iter
+        self.launches = 0
+        self._graphs = {}
+        self.stop = stop
+        D.barrier()
+
+    def iterate(self, n, use_graph=True):
+        L = nv.lib()
+        if use_graph and n >= 8:
+            g = self._graphs.get(n)
+            if g is None:
+                # first launch outside capture sets the kernel attributes
+                torch.cuda.synchronize(self.dev)
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g):
+                    nv.check(L.gadmm_star_iterate(C.byref(self.p), int(n), nv.stream_ptr()))
+                self._graphs[n] = g
+            g.replay()
+        else:
+            nv.check(L.gadmm_star_iterate(C.byref(self.p), int(n), nv.stream_ptr()))
+        self.launches += 2 * n
+
+    def run(self, num_iter=None, window=64):
+        T = self.max_iter if num_iter is None else min(int(num_iter), self.max_iter)
+        self.iterate(1, use_graph=False)
+        done = 1
+        while done < T:
+            if self.stop and int(self.ctrl[1].item()):
+                break
+            n = min(window, T - done)
+            self.iterate(n)
+            done += n
+        torch.cuda.synchronize(self.dev)
+        hit = int(self.ctrl[1].item())
+        return hit if hit else T
+
+    def results(self, Iter):
+        obj = self.obj_hist[1:Iter + 1].cpu().numpy()
+        loss = self.loss_hist[1:Iter + 1].cpu().numpy()
+        t = self.t_hist[1:Iter + 1].to(torch.float64)
+        tv = (t - t[0]) * 1e-9
+        if self.dist.world > 1:
+            import torch.distributed as dist
+            dist.all_reduce(tv, op=dist.ReduceOp.MAX)
+        return obj, loss, Iter, tv.cpu().numpy()
+
+
+def star_admm(XX, YY, rho, no_workers, num_feature, noSamples, num_iter, obj0, acc, store="f64",
+              dist=None, window=64, return_engine=False):
+    eng = StarEngine(XX, YY, rho, no_workers, num_feature, noSamples, num_iter, obj0, acc, dist=dist,
+                     store=store)
+    it = eng.run(num_iter, window=window)
+    res = eng.results(it)
+    return res + (eng,) if return_engine else res

@@ -117,3 +117,28 @@ class GadmmOwn(C.Structure):
 
 
 FO_GD, FO_LAG_PS, FO_LAG_WK, FO_IAG_CYCLIC, FO_IAG_RANDOM = range(5)
+
+
+class GadmmStar(C.Structure):
+    """Mirror of ``struct GadmmStar`` (include/gadmm_b200.h)."""
+    _fields_ = [
+        ("Mptr", _vp), ("Ms", _vp), ("b", _vp), ("hyy", _vp), ("bs", _vp), ("lam", _vp),
+        ("theta", _vp), ("z", _vp), ("U", _vp), ("fw", _vp), ("ubuf", _vp), ("uflag", _vp),
+        ("ubuf_peer", _vp), ("uflag_peer", _vp), ("rowpart", _vp), ("colpart", _vp),
+        ("counters", _vp), ("ctrl", _vp), ("obj_hist", _vp), ("loss_hist", _vp), ("t_hist", _vp),
+        ("rho", C.c_double), ("obj0", C.c_double), ("acc", C.c_double), ("hyy_s", C.c_double),
+        ("d", C.c_int), ("dp", C.c_int), ("N", C.c_int), ("Nw", C.c_int), ("rank", C.c_int),
+        ("nranks", C.c_int), ("store", C.c_int), ("max_iter", C.c_int),
+    ]
+
+
+class GadmmLogistic(C.Structure):
+    """Mirror of ``struct GadmmLogistic`` (include/gadmm_b200.h)."""
+    _fields_ = [
+        ("X", _vp), ("y", _vp), ("theta", _vp), ("lam", _vp), ("fw", _vp), ("inner_steps", _vp),
+        ("ctrl", _vp), ("counters", _vp), ("obj_hist", _vp), ("loss_hist", _vp), ("t_hist", _vp),
+        ("rho", C.c_double), ("lam_log", C.c_double), ("gd_step", C.c_double),
+        ("inner_tol", C.c_double), ("obj0", C.c_double), ("acc", C.c_double),
+        ("N", C.c_int), ("s", C.c_int), ("d", C.c_int), ("dp", C.c_int), ("max_iter", C.c_int),
+        ("max_inner", C.c_int),
+    ]

@@ -178,6 +178,71 @@ int gadmm_dgd_update(const GadmmOwn* p, void* stream);
  * averaging sweep; update=0: record only (closes the last iteration). */
 int gadmm_dualavg_update(const GadmmOwn* p, int update, void* stream);
 
+/* ---- standard (star) ADMM (K6; standared_ADMM.m:17-107) ------------------------------------
+ * Two launches per iteration.  Workers kernel: theta_n = M_n (b_n - lambda_n + rho z) for the
+ * N-1 workers (lambda_n += rho(theta_n - z) of the previous iteration is folded into the RHS
+ * assembly), per-worker objective, and -- by the last CTA -- the reduction
+ * u = sum_n (lambda_n + rho theta_n), pushed with P2P stores + a release flag into every GPU.
+ * Server kernel (replicated on every GPU, so no broadcast is needed): waits for all ranks'
+ * partials, z = M_s (b_s + u), total objective, stop test, iteration counter. */
+typedef struct GadmmStar {
+  const void* const* Mptr;   /* [Nw] packed (G_n + rho I)^-1 of the local workers */
+  const void* Ms;            /* packed (G_s + (N-1) rho I)^-1 of the server shard (replicated) */
+  const double* b;           /* [Nw][dp] */
+  const double* hyy;         /* [Nw] */
+  const double* bs;          /* [dp] server shard */
+  double* lam;               /* [Nw][dp] */
+  double* theta;             /* [Nw][dp] */
+  double* z;                 /* [dp] */
+  double* U;                 /* [Nw][dp] scratch: lambda_n + rho theta_n */
+  double* fw;                /* [Nw] */
+  double* ubuf;              /* symmetric: [2][nranks][dp+64] partial u (+ objective at [dp]) */
+  unsigned long long* uflag; /* symmetric: [2][nranks] */
+  double* const* ubuf_peer;  /* [nranks] */
+  unsigned long long* const* uflag_peer;
+  double* rowpart;           /* [Nw+1][dp] (last slot: server solve) */
+  double* colpart;           /* [Nw+1][colpart elems] */
+  unsigned int* counters;    /* [Nw+2] zero-initialised */
+  unsigned long long* ctrl;  /* [0]=iteration, [1]=hit, [2]=stop enabled */
+  double* obj_hist;
+  double* loss_hist;
+  unsigned long long* t_hist;
+  double rho, obj0, acc, hyy_s;
+  int d, dp, N, Nw, rank, nranks, store, max_iter;
+} GadmmStar;
+int gadmm_star_iterate(const GadmmStar* p, int n_iter, void* stream);
+
+/* ---- logistic GADMM, inexact local solves (K9; group_ADMM_logistic_GD.m, logReg_GD.m) ------- */
+typedef struct GadmmLogistic {
+  const double* X;           /* [N][s][d] */
+  const double* y;           /* [N][s]   labels +-1 */
+  double* theta;             /* [N][dp] */
+  double* lam;               /* [N][dp]  edge duals: lam[n] couples workers n and n+1 */
+  const double* fw;          /* [N] per-worker objective (from gadmm_logistic_grad) */
+  unsigned long long* inner_steps; /* optional: total inner GD steps */
+  unsigned long long* ctrl;  /* [0]=iteration, [1]=hit, [2]=stop enabled */
+  unsigned int* counters;    /* [1] zero-initialised */
+  double* obj_hist;
+  double* loss_hist;
+  unsigned long long* t_hist;
+  double rho, lam_log, gd_step, inner_tol, obj0, acc;
+  int N, s, d, dp, max_iter, max_inner;
+} GadmmLogistic;
+int gadmm_logistic_half_gd(const GadmmLogistic* p, int color, void* stream);
+int gadmm_logistic_dual_obj(const GadmmLogistic* p, void* stream);
+
+/* ---- topology and synthetic data on the device (K10, K13, K14) -------------------------------
+ * Philox4x32-10 fills (seed, stream_id) -> reproducible; out[i] = scale*U[0,1) / N(mean, sd). */
+int gadmm_philox_uniform(double* out, size_t n, unsigned long long seed, unsigned int stream_id,
+                         double scale, void* stream);
+int gadmm_philox_normal(void* out, size_t n, int is_f32, unsigned long long seed,
+                        unsigned int stream_id, double mean, double sd, void* stream);
+/* Greedy nearest-neighbour chain from node 0 over positions xy[N][2] (findPath.m:16-30; model 1 =
+ * findPath2.m: energy costs, P_central, centre node).  path: N ints (0-based), cost: N-1,
+ * d_square (optional): N*N, P_central (optional): N, center (optional): 1 int. */
+int gadmm_find_path(const double* xy, int N, int model, int* path, double* cost, double* d_square,
+                    double* P_central, int* center, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
