@@ -1,0 +1,318 @@
+// Gram / weighted Gram on the 5th-generation tensor cores (K1 of SURVEY.md section 2.4):
+//     G_n += X_n' diag(w) X_n        (w = 1: X'X of group_ADMM_closedForm.m:43; w = sigma(1-sigma):
+//                                     the logistic Hessian X'DX of the Newton local solve)
+//
+// tcgen05 has no fp64 kind, so every fp32 value is split x = hi + lo with hi, lo exactly
+// representable in tf32 and the product is formed as hi*hi' + hi*lo' + lo*hi' (3 MMAs of
+// kind::tf32 into one fp32 TMEM accumulator, error ~2^-21 per product).  To keep the fp32
+// accumulation short, the sample dimension is cut into segments of KSEG samples; each CTA owns
+// one (128x128 output tile, segment) and adds its tile into the fp64 result with RED.ADD.F64.
+//
+// Data path: a prep kernel writes the (optionally sqrt(w)-scaled) shard transposed and split,
+// Xt_hi / Xt_lo [N][dT][sP] fp32 with samples contiguous (K-major for both MMA operands, since
+// A and B are row blocks of the same matrix).  The main kernel is warp specialised:
+//   warp 0  TMA producer   cp.async.bulk.tensor.3d (box 32 x 128, SWIZZLE_128B) -> 3-stage ring
+//   warp 1  MMA issuer     one elected lane: 4 k-steps x 3 split products per stage,
+//                          tcgen05.commit frees the stage / signals the epilogue; owns TMEM alloc
+//   warps 2-5 epilogue     tcgen05.ld 32x32b (each warp its TMEM lane quarter) -> fp64 atomics,
+//                          mirrored for off-diagonal tiles
+// Diagonal tiles load only the A operand (B descriptor aliases it).
+#include "../include/gadmm_b200.h"
+#include "common.cuh"
+
+#include <cuda.h>
+
+namespace gadmm {
+
+constexpr int GT = 128;        // output tile edge (UMMA M = N = 128)
+constexpr int GBK = 32;        // fp32 elements per k-chunk = one 128-byte swizzle row
+constexpr int GSTAGES = 3;
+constexpr int GTILE_BYTES = GT * GBK * 4;        // 16 KiB per operand tile
+constexpr int GSTAGE_BYTES = 4 * GTILE_BYTES;    // A_hi, A_lo, B_hi, B_lo
+constexpr int GTHREADS = 192;
+constexpr int GSMEM = GSTAGES * GSTAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
+
+__device__ __forceinline__ float tf32_round(float x) {
+  uint32_t u;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(x));
+  return __uint_as_float(u);
+}
+
+// X: [N][s][d] (fp64 or fp32) -> Xt_hi, Xt_lo: [N][dT][sP] fp32, zero padded, optionally scaled by
+// sqrt(w[n][r]).  32x32 smem transpose: coalesced reads along d, coalesced writes along s.
+template <typename TIn>
+__global__ void __launch_bounds__(256)
+split_transpose_kernel(const TIn* __restrict__ X, const double* __restrict__ w, int s, int d, int sP,
+                       int dT, float* __restrict__ hi, float* __restrict__ lo) {
+  __shared__ float tile[32][33];
+  const int n = blockIdx.z, r0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const TIn* Xn = X + (size_t)n * s * d;
+  for (int i = ty; i < 32; i += 8) {
+    const int r = r0 + i, c = c0 + tx;
+    float v = 0.f;
+    if (r < s && c < d) {
+      double x = (double)Xn[(size_t)r * d + c];
+      if (w) x *= sqrt(w[(size_t)n * s + r]);
+      v = (float)x;
+    }
+    tile[i][tx] = v;
+  }
+  __syncthreads();
+  for (int i = ty; i < 32; i += 8) {
+    const int c = c0 + i, r = r0 + tx;      // output row = feature c, column = sample r
+    if (c < dT && r < sP) {
+      const float v = tile[tx][i];
+      const float h = tf32_round(v);
+      const size_t o = ((size_t)n * dT + c) * sP + r;
+      hi[o] = h;
+      lo[o] = tf32_round(v - h);
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------ PTX wrappers
+__device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* map, uint64_t* bar, int c0,
+                                            int c1, int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4, %5}], [%2];" ::"r"(smem_u32(dst)),
+      "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() {
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tc_fence_after() {
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tc_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
+                   smem_u32(bar))
+               : "memory");
+}
+// D[tmem] (+)= A[smem desc] * B[smem desc]^T, kind::tf32, fp32 accumulate
+__device__ __forceinline__ void tc_mma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc,
+                                            uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// K-major, SWIZZLE_128B operand tile: rows of 128 B, 8-row groups 1024 B apart.
+__device__ __forceinline__ uint64_t umma_desc_sw128(const void* smem) {
+  const uint32_t a = smem_u32(smem);
+  uint64_t d = 0;
+  d |= (uint64_t)((a >> 4) & 0x3FFF);              // start address  [0,14)
+  d |= (uint64_t)1 << 16;                          // leading byte offset (unused for SW128 K-major)
+  d |= (uint64_t)(1024 >> 4) << 32;                // stride byte offset [32,46)
+  d |= (uint64_t)1 << 46;                          // descriptor version (sm_100)
+  d |= (uint64_t)2 << 61;                          // SWIZZLE_128B
+  return d;
+}
+__device__ __forceinline__ void tmem_ld_32x32b_x32(uint32_t taddr, uint32_t (&v)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]),
+        "=r"(v[7]), "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]),
+        "=r"(v[14]), "=r"(v[15]), "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]),
+        "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]),
+        "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+      : "r"(taddr)
+      : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// idesc: c=F32 (1<<4), a=b=TF32 (2<<7, 2<<10), K-major both, N>>3 at [17,23), M>>4 at [24,29)
+constexpr uint32_t kIdescTf32 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(GT >> 3) << 17) |
+                                ((uint32_t)(GT >> 4) << 24);
+
+// grid: (lower-triangular 128-tiles, k-segments, N)
+__global__ void __launch_bounds__(GTHREADS, 1)
+gram_tcgen05_kernel(const __grid_constant__ CUtensorMap map_hi,
+                    const __grid_constant__ CUtensorMap map_lo, int sP, int kseg, int dp,
+                    double* __restrict__ G) {
+  extern __shared__ unsigned char gsm_raw[];
+  unsigned char* base =
+      reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(gsm_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full = reinterpret_cast<uint64_t*>(base + GSTAGES * GSTAGE_BYTES);
+  uint64_t* empty = full + GSTAGES;
+  uint64_t* acc_full = empty + GSTAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_full + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  int I = 0, rem = blockIdx.x;
+  while (rem > I) { rem -= I + 1; ++I; }
+  const int J = rem, n = blockIdx.z;
+  const bool diag = (I == J);
+  const int k_begin = blockIdx.y * kseg;
+  const int k_end = min(sP, k_begin + kseg);
+  const int nchunks = (k_end - k_begin) / GBK;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < GSTAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+    mbar_init(acc_full, 1);
+    mbar_fence_init();
+  }
+  if (warp == 1) {   // TMEM: 128 fp32 accumulator columns
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                     smem_u32(tmem_slot)),
+                 "r"(128)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int c = 0; c < nchunks; ++c) {
+        mbar_wait(&empty[stage], phase ^ 1);
+        unsigned char* st = base + stage * GSTAGE_BYTES;
+        const int k0 = k_begin + c * GBK;
+        mbar_arrive_expect_tx(&full[stage], diag ? 2 * GTILE_BYTES : 4 * GTILE_BYTES);
+        tma_load_3d(st, &map_hi, &full[stage], k0, I * GT, n);
+        tma_load_3d(st + GTILE_BYTES, &map_lo, &full[stage], k0, I * GT, n);
+        if (!diag) {
+          tma_load_3d(st + 2 * GTILE_BYTES, &map_hi, &full[stage], k0, J * GT, n);
+          tma_load_3d(st + 3 * GTILE_BYTES, &map_lo, &full[stage], k0, J * GT, n);
+        }
+        if (++stage == GSTAGES) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int c = 0; c < nchunks; ++c) {
+        mbar_wait(&full[stage], phase);
+        tc_fence_after();
+        unsigned char* st = base + stage * GSTAGE_BYTES;
+        const uint64_t a_hi = umma_desc_sw128(st), a_lo = umma_desc_sw128(st + GTILE_BYTES);
+        const uint64_t b_hi = diag ? a_hi : umma_desc_sw128(st + 2 * GTILE_BYTES);
+        const uint64_t b_lo = diag ? a_lo : umma_desc_sw128(st + 3 * GTILE_BYTES);
+#pragma unroll
+        for (int k = 0; k < GBK / 8; ++k) {                 // UMMA_K = 8 tf32 = 32 bytes
+          const uint64_t adv = (uint64_t)((k * 32) >> 4);   // start-address field advance
+          tc_mma_tf32(tmem, a_hi + adv, b_hi + adv, kIdescTf32, (c | k) != 0);
+          tc_mma_tf32(tmem, a_hi + adv, b_lo + adv, kIdescTf32, 1u);
+          tc_mma_tf32(tmem, a_lo + adv, b_hi + adv, kIdescTf32, 1u);
+        }
+        tc_commit(&empty[stage]);                            // frees the smem stage when MMAs retire
+        if (++stage == GSTAGES) { stage = 0; phase ^= 1; }
+      }
+      tc_commit(acc_full);                                   // accumulator complete
+    }
+  } else {
+    // ---- epilogue: warps 2..5 own TMEM lane quarters (warp id % 4)
+    const int q = warp & 3;
+    mbar_wait(acc_full, 0);
+    tc_fence_after();
+    const int m = q * 32 + lane;                             // row inside the tile
+    double* Gn = G + (size_t)n * dp * dp;
+    const size_t grow = (size_t)I * GT + m;
+    if (nchunks > 0) {
+      for (int cb = 0; cb < GT; cb += 32) {
+        uint32_t v[32];
+        tmem_ld_32x32b_x32(tmem + ((uint32_t)(q * 32) << 16) + cb, v);
+        if (grow < (size_t)dp) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const size_t gcol = (size_t)J * GT + cb + j;
+            if (gcol >= (size_t)dp) continue;
+            if (diag && gcol > grow) continue;               // lower triangle of diagonal tiles
+            const double val = (double)__uint_as_float(v[j]);
+            atomicAdd(Gn + grow * dp + gcol, val);
+            if (gcol != grow) atomicAdd(Gn + gcol * dp + grow, val);
+          }
+        }
+      }
+    }
+    tc_fence_before();
+  }
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(128)
+                 : "memory");
+  }
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static int make_map(CUtensorMap* map, const float* ptr, int N, int dT, int sP) {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    cudaDriverEntryPointQueryResult qres;
+    void* p = nullptr;
+    GADMM_CUDA_OK(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres));
+    GADMM_REQUIRE(p && qres == cudaDriverEntryPointSuccess, "cuTensorMapEncodeTiled not available");
+    fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  const cuuint64_t dims[3] = {(cuuint64_t)sP, (cuuint64_t)dT, (cuuint64_t)N};
+  const cuuint64_t strides[2] = {(cuuint64_t)sP * 4, (cuuint64_t)sP * dT * 4};
+  const cuuint32_t box[3] = {GBK, GT, 1};
+  const cuuint32_t estr[3] = {1, 1, 1};
+  const CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(ptr), dims,
+                        strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                        CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  GADMM_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+  return 0;
+}
+
+}  // namespace gadmm
+
+using namespace gadmm;
+
+extern "C" {
+
+size_t gadmm_gram_tc_workspace_floats(int N, int s, int d) {
+  const size_t dT = (size_t)(d + GT - 1) / GT * GT, sP = (size_t)(s + GBK - 1) / GBK * GBK;
+  return 2 * (size_t)N * dT * sP;
+}
+
+int gadmm_gram_tcgen05(const void* X, int x_is_f32, const double* w, int N, int s, int d, int dp,
+                       float* work, double* G, int accumulate, int kseg, void* stream) {
+  GADMM_REQUIRE(N > 0 && s > 0 && d > 0 && dp >= d && dp % 64 == 0, "gram_tcgen05: bad shape");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int dT = (d + GT - 1) / GT * GT, sP = (s + GBK - 1) / GBK * GBK;
+  if (kseg <= 0) kseg = 2048;
+  kseg = (kseg + GBK - 1) / GBK * GBK;
+  float* hi = work;
+  float* lo = work + (size_t)N * dT * sP;
+  dim3 pg((sP + 31) / 32, (dT + 31) / 32, N);
+  if (x_is_f32)
+    split_transpose_kernel<float><<<pg, 256, 0, st>>>((const float*)X, w, s, d, sP, dT, hi, lo);
+  else
+    split_transpose_kernel<double><<<pg, 256, 0, st>>>((const double*)X, w, s, d, sP, dT, hi, lo);
+  GADMM_CUDA_OK(cudaGetLastError());
+  if (!accumulate) GADMM_CUDA_OK(cudaMemsetAsync(G, 0, (size_t)N * dp * dp * sizeof(double), st));
+  CUtensorMap mh, ml;
+  if (int e = make_map(&mh, hi, N, dT, sP)) return e;
+  if (int e = make_map(&ml, lo, N, dT, sP)) return e;
+  static bool configured = false;
+  if (!configured) {
+    GADMM_CUDA_OK(cudaFuncSetAttribute(gram_tcgen05_kernel,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, GSMEM));
+    configured = true;
+  }
+  const int nB = dT / GT;
+  dim3 grid(nB * (nB + 1) / 2, (sP + kseg - 1) / kseg, N);
+  gram_tcgen05_kernel<<<grid, GTHREADS, GSMEM, st>>>(mh, ml, sP, kseg, dp, G);
+  GADMM_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+}  // extern "C"

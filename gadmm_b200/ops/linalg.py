@@ -29,6 +29,34 @@ def gram(X: torch.Tensor, y: torch.Tensor, dp: int = None):
     return G, b, hyy
 
 
+def gram_tc(X: torch.Tensor, dp: int = None, w: torch.Tensor = None, out: torch.Tensor = None,
+            accumulate: bool = False, kseg: int = 0):
+    """``G_n (+)= X_n' diag(w_n) X_n`` on the tcgen05 tensor cores (split-tf32, fp32-grade accuracy,
+    fp64 result).  X: (N, s, d) float64 or float32 CUDA; w: optional (N, s) float64 row weights."""
+    N, s, d = X.shape
+    dp = nv.padded(d) if dp is None else dp
+    X = X.contiguous()
+    L = nv.lib()
+    L.gadmm_gram_tc_workspace_floats.restype = C.c_size_t
+    nwork = int(L.gadmm_gram_tc_workspace_floats(N, s, d))
+    work = torch.empty((nwork,), dtype=torch.float32, device=X.device)
+    G = torch.empty((N, dp, dp), dtype=torch.float64, device=X.device) if out is None else out
+    nv.check(L.gadmm_gram_tcgen05(nv.ptr(X), 1 if X.dtype == torch.float32 else 0,
+                                  nv.ptr(w.contiguous() if w is not None else None), N, s, d, dp,
+                                  nv.ptr(work), nv.ptr(G), 1 if accumulate else 0, int(kseg),
+                                  nv.stream_ptr()))
+    return G
+
+
+def xty(X: torch.Tensor, y: torch.Tensor, dp: int):
+    """``b_n = X_n' y_n`` and ``0.5 y'y`` in fp64 (companion of :func:`gram_tc`)."""
+    N, s, d = X.shape
+    Xd = X if X.dtype == torch.float64 else X.double()
+    b = torch.zeros((N, dp), dtype=torch.float64, device=X.device)
+    b[:, :d] = torch.einsum("nsd,ns->nd", Xd, y)
+    return b, 0.5 * (y * y).sum(1)
+
+
 def shifted_inverse(G: torch.Tensor, d: int, shift: float, out: torch.Tensor = None):
     """``(G_n + shift*I)^-1`` for a batch of padded Gram matrices; lower block-triangle is valid.
 

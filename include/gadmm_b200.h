@@ -231,6 +231,14 @@ typedef struct GadmmLogistic {
 int gadmm_logistic_half_gd(const GadmmLogistic* p, int color, void* stream);
 int gadmm_logistic_dual_obj(const GadmmLogistic* p, void* stream);
 
+/* ---- tensor-core Gram (K1 proper): G[n] (+)= X_n' diag(w_n) X_n with tcgen05 kind::tf32 in a
+ * 3-product hi/lo split (fp32-grade), TMA-fed, TMEM accumulators, fp64 result.  X: [N][s][d] fp64
+ * or fp32; w: optional [N][s] row weights (logistic Hessian X'DX); work: gadmm_gram_tc_workspace_floats
+ * floats; kseg: samples per fp32 accumulation segment (0 = 2048). */
+size_t gadmm_gram_tc_workspace_floats(int N, int s, int d);
+int gadmm_gram_tcgen05(const void* X, int x_is_f32, const double* w, int N, int s, int d, int dp,
+                       float* work, double* G, int accumulate, int kseg, void* stream);
+
 /* ---- topology and synthetic data on the device (K10, K13, K14) -------------------------------
  * Philox4x32-10 fills (seed, stream_id) -> reproducible; out[i] = scale*U[0,1) / N(mean, sd). */
 int gadmm_philox_uniform(double* out, size_t n, unsigned long long seed, unsigned int stream_id,

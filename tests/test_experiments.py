@@ -1,0 +1,46 @@
+"""The seven drivers run end to end on the oracle backend (shrunk) and emit the reference's arrays."""
+import numpy as np
+
+from gadmm_b200.experiments import (dgadmm_real, dgadmm_synth, gadmm_vs_admm, linreg_real,
+                                    linreg_synth, logreg_real, logreg_synth)
+
+
+def test_linreg_synth(tmp_path):
+    cfg = linreg_synth.Config(num_workers=6, num_sample=12, num_iter_baselines=300,
+                              num_iter_gadmm=2000, backend="oracle")
+    curves, summ = linreg_synth.run(cfg)
+    for rho in (3, 5, 7):
+        assert summ[f"Iter_rho{rho}"] < 2000
+        n = summ[f"Iter_rho{rho}"]
+        np.testing.assert_array_equal(curves[f"cumulative_com_GADMM_rho{rho}"], 6 * np.arange(1, n + 1))
+    assert curves["cumulative_com_GD"][2] == 3 * 6 + 3 and curves["loss_LAG_PS"].shape == (300,)
+    from gadmm_b200.io import save_curves
+    save_curves(str(tmp_path / "c.mat"), curves)
+
+
+def test_linreg_real_and_dgadmm_real():
+    c, s = linreg_real.run(linreg_real.Config(num_iter_baselines=200, num_iter_gadmm=50, backend="oracle"))
+    assert s["N"] == 10 and s["surrogate_data"] and c["loss_GADMM_rho3"].shape[0] <= 50
+    c, s = dgadmm_real.run(dgadmm_real.Config(num_iter=300, backend="oracle"))
+    assert c["com_cost_d"].shape == c["loss_GADMM_d"].shape
+
+
+def test_logreg_drivers():
+    c, s = logreg_synth.run(logreg_synth.Config(num_workers=4, num_sample=10, num_iter_baselines=400,
+                                                num_iter_dualavg=50, num_iter_gadmm=30, lam=1e-3,
+                                                rhos=(0.01,), gd_step=0.5, backend="oracle"))
+    assert "loss_GADMM_rho0.01" in c and c["obj_GD"].shape == (400,)
+    c, s = logreg_real.run(logreg_real.Config(num_iter_baselines=300, num_iter_dualavg=50,
+                                              num_iter_gadmm=20, backend="oracle"))
+    assert s["N"] == 10 and s["d"] == 34
+
+
+def test_dgadmm_synth_and_vs_admm():
+    c, s = dgadmm_synth.run(dgadmm_synth.Config(num_workers=8, num_sample=12, n_topologies=700,
+                                                num_iter=3000, taus_b=(1e9, 10), backend="oracle"))
+    assert s["Iter_dgadmm_v0"] <= s["Iter_static"]
+    n = s["Iter_dgadmm_v0"]
+    assert c["cumulative_com_GADMM_rho3_d0"].shape == (n,)
+    c, s = gadmm_vs_admm.run(gadmm_vs_admm.Config(num_workers=8, num_sample=12, num_iter=4000,
+                                                  taus=(10,), backend="oracle"))
+    assert s["cost_star"] > 0 and c["cumulative_com_ADMM"][0] == s["cost_star"]

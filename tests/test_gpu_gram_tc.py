@@ -1,0 +1,36 @@
+"""tcgen05 split-tf32 Gram vs a plain fp64 PyTorch reference."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("N,s,d,dtype", [(2, 64, 128, torch.float32), (3, 50, 50, torch.float64),
+                                         (1, 700, 300, torch.float32), (2, 4500, 256, torch.float32)])
+def test_gram_tc_matches_fp64(N, s, d, dtype):
+    from gadmm_b200.ops import linalg as LA
+    dev = torch.device("cuda", 0)
+    g = torch.Generator(device="cpu").manual_seed(N * 1000 + s)
+    X = torch.randn(N, s, d, dtype=dtype, generator=g).to(dev)
+    G = LA.gram_tc(X)
+    dp = G.shape[1]
+    Xd = X.double()
+    ref = Xd.transpose(1, 2) @ Xd
+    scale = ref.abs().max()
+    err = (G[:, :d, :d] - ref).abs().max() / scale
+    assert err < 2e-6, float(err)
+    assert torch.count_nonzero(G[:, d:, :]) == 0 and torch.count_nonzero(G[:, :, d:]) == 0
+    torch.testing.assert_close(G, G.transpose(1, 2), rtol=0, atol=0)   # exactly symmetric
+
+
+def test_gram_tc_weighted_and_accumulate():
+    from gadmm_b200.ops import linalg as LA
+    dev = torch.device("cuda", 0)
+    g = torch.Generator(device="cpu").manual_seed(5)
+    X = torch.randn(2, 333, 200, dtype=torch.float64, generator=g).to(dev)
+    w = torch.rand(2, 333, dtype=torch.float64, generator=g).to(dev)
+    G = LA.gram_tc(X, w=w)
+    ref = (X * w.unsqueeze(2)).transpose(1, 2) @ X
+    assert ((G[:, :200, :200] - ref).abs().max() / ref.abs().max()) < 2e-6
+    G2 = LA.gram_tc(X, w=w, out=G.clone(), accumulate=True)
+    assert ((G2[:, :200, :200] - 2 * ref).abs().max() / ref.abs().max()) < 4e-6
