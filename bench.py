@@ -13,6 +13,8 @@ so no L2 flush is needed between steps).
     python bench.py --impl reference      # the MATLAB reference cannot run here -> "unavailable"
 """
 import argparse
+import os as _os
+_os.environ["NCCL_DEBUG"] = _os.environ.get("GADMM_NCCL_DEBUG", "WARN")  # keep stdout to the one JSON line
 import json
 import os
 import subprocess
