@@ -14,7 +14,7 @@ so no L2 flush is needed between steps).
 """
 import argparse
 import os as _os
-_os.environ["NCCL_DEBUG"] = _os.environ.get("GADMM_NCCL_DEBUG", "WARN")  # keep stdout to the one JSON line
+_os.environ.pop("NCCL_DEBUG", None)   # NCCL prints its version banner on stdout otherwise
 import json
 import os
 import subprocess
@@ -38,6 +38,9 @@ def parse():
     ap.add_argument("--store", default="f64", choices=["f64", "f32"])
     ap.add_argument("--e2e-steps", type=int, default=0, help="0 = same as --steps")
     ap.add_argument("--verbose", action="store_true")
+    ap.add_argument("--gram", default="f64", choices=["f64", "tc"],
+                    help="setup Gram: fp64 SIMT or tcgen05 split-tf32 (sample-heavy shards)")
+    ap.add_argument("--no-graph", action="store_true", help="launch kernels one by one")
     return ap.parse_args()
 
 
@@ -118,22 +121,28 @@ def main():
 
     if a.impl == "nccl":
         from gadmm_b200.parallel.nccl_baseline import NcclChainGadmm as Engine
-        eng = Engine(N, d, a.rho, 0.0, 1e-4, a.warmup + a.steps + 8, dist=D)
+        eng = Engine(N, d, a.rho, 0.0, 1e-4, a.warmup + 2 * a.steps + 8, dist=D)
         from gadmm_b200.parallel.nccl_baseline import build_scaled_linreg
     else:
         from gadmm_b200.engine.chain import ChainEngine
         from gadmm_b200.engine.scaled import build_scaled_linreg
         es = a.e2e_steps or a.steps
-        eng = ChainEngine(N, d, a.rho, 0.0, 1e-4, a.warmup + a.steps + es + 8, dist=D,
+        eng = ChainEngine(N, d, a.rho, 0.0, 1e-4, a.warmup + 2 * a.steps + es + 8, dist=D,
                           store=a.store, dynamic=False, stop=False)
-    obj0 = build_scaled_linreg(eng, s, seed=0, verbose=a.verbose)
+    kw = {"gram": a.gram} if a.impl == "b200" else {}
+    obj0 = build_scaled_linreg(eng, s, seed=0, verbose=a.verbose, **kw)
     eng.set_path(np.arange(N))
     torch.cuda.synchronize()
     D.barrier()
     setup_s = time.time() - t_setup0
 
     # ---- warm-up (untimed), then exactly K timed steps; device clock, max over ranks
+    # The K-step window is captured once as a CUDA graph (3 kernels per step, device-resident
+    # iteration counter) and replayed; capture + first replay are part of the warm-up.
+    graph = not a.no_graph
     eng.iterate(a.warmup, use_graph=False)
+    if graph:
+        eng.iterate(a.steps, use_graph=True)
     torch.cuda.synchronize()
     D.barrier()
     sampler = ClockSampler(local)
@@ -145,7 +154,7 @@ def main():
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     l0 = getattr(eng, "launches", 0)
     e0.record()
-    eng.iterate(a.steps, use_graph=False)
+    eng.iterate(a.steps, use_graph=graph)
     e1.record()
     torch.cuda.synchronize()
     D.barrier()
@@ -171,11 +180,13 @@ def main():
                "h2d_bytes_per_step": eng.step_h2d_bytes, "d2h_bytes_per_step": eng.step_d2h_bytes,
                "last_loss": last[1]}
 
-    obj, loss, it, tv = eng.results(a.warmup + a.steps)
+    obj, loss, it, tv = eng.results(a.warmup + (2 if graph else 1) * a.steps)
     if rank == 0:
         elt = 8 if a.store == "f64" else 4
-        nT = eng.dp // 64
+        nT = (d + 63) // 64
         bytes_per_step = N * (nT * (nT + 1) // 2) * 64 * 64 * elt
+        if a.impl == "nccl":
+            bytes_per_step = N * d * d * 8       # dense fp64 inverses through cuBLAS bmm
         peaks = {}
         try:
             peaks = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)),
@@ -192,7 +203,7 @@ def main():
             "scaling": "strong", "vs_baseline": None, "dtype": "fp64" if a.store == "f64"
             else "fp32-storage/fp64-accumulate", "data": "synthetic", "impl": a.impl,
             "config": {"model": "GADMM closed-form linear regression (group_ADMM_closedForm)",
-                       "workers": N, "d": d, "samples_per_worker": s, "rho": a.rho,
+                       "workers": N, "d": d, "samples_per_worker": s, "rho": a.rho, "setup_gram": a.gram,
                        "global_batch": N * s, "seq_len": d,
                        "parallelism": f"chain-segments x{world} (consensus DP)",
                        "l2": "inputs larger than L2: every step streams all packed inverses "

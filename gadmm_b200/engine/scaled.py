@@ -16,11 +16,14 @@ from .chain import ChainEngine
 
 
 def build_scaled_linreg(eng: ChainEngine, s: int, seed: int = 0, noise: float = 0.1,
-                        batch: int = 0, verbose: bool = False):
+                        batch: int = 0, verbose: bool = False, gram: str = "f64",
+                        s_chunk: int = 32768):
     """Fill ``eng`` with a synthetic least-squares problem; returns ``obj0`` (global optimum).
 
     The optimum needs ``sum_n G_n`` and ``sum_n b_n``; they are accumulated per rank and summed
     with one NCCL all-reduce (plumbing, outside any timed region)."""
+    if gram == "tc":
+        return _build_scaled_tc(eng, s, seed, noise, verbose, s_chunk)
     dev, d, dp = eng.dev, eng.d, eng.dp
     gen = torch.Generator(device=dev)
     gen.manual_seed(1234)
@@ -47,6 +50,55 @@ def build_scaled_linreg(eng: ChainEngine, s: int, seed: int = 0, noise: float = 
         del G
         if verbose and eng.dist.rank == 0:
             print(f"  setup: workers {k0 + nb}/{eng.Nloc}", flush=True)
+    eng.dist.all_reduce_sum_(Gsum)
+    eng.dist.all_reduce_sum_(bsum)
+    eng.dist.all_reduce_sum_(hsum)
+    A = LA.shifted_inverse(Gsum.unsqueeze(0), d, 0.0)
+    P = LA.pack_sym(A, d)
+    th = LA.BatchedSymv(P, dp)(bsum.unsqueeze(0))[0]
+    obj0 = 0.5 * float(th @ (Gsum @ th)) - float(bsum @ th) + float(hsum)
+    eng.obj0 = obj0
+    eng._desc = None
+    return obj0
+
+
+def _build_scaled_tc(eng: ChainEngine, s: int, seed: int, noise: float, verbose: bool,
+                     s_chunk: int):
+    """Tensor-core path for sample-heavy shards (BASELINE.json config 5: 1M samples x d=16384 per
+    worker): the shard is drawn chunk by chunk in fp32 with the Philox kernel, every chunk is
+    folded into ``G_n`` by the tcgen05 split-tf32 Gram (``accumulate=True``) and dropped."""
+    from ..ops.topology import philox_normal
+    dev, d, dp = eng.dev, eng.d, eng.dp
+    theta_true = philox_normal((d,), seed=1234, stream_id=7, dtype=torch.float32, device=dev)
+    Gsum = torch.zeros((dp, dp), dtype=torch.float64, device=dev)
+    bsum = torch.zeros((dp,), dtype=torch.float64, device=dev)
+    hsum = torch.zeros((), dtype=torch.float64, device=dev)
+    sd = 1.0 / np.sqrt(s)
+    nb_max = max(1, min(eng.Nloc, int(2e9 // (min(s, s_chunk) * d * 4))))
+    for k0 in range(0, eng.Nloc, nb_max):
+        nb = min(nb_max, eng.Nloc - k0)
+        G = torch.zeros((nb, dp, dp), dtype=torch.float64, device=dev)
+        b = torch.zeros((nb, dp), dtype=torch.float64, device=dev)
+        hyy = torch.zeros((nb,), dtype=torch.float64, device=dev)
+        for c0 in range(0, s, s_chunk):
+            sc = min(s_chunk, s - c0)
+            X = philox_normal((nb, sc, d), seed=seed * 1000003 + int(eng.gids[k0]),
+                              stream_id=1 + c0 // s_chunk, sd=sd, dtype=torch.float32, device=dev)
+            y = torch.matmul(X, theta_true)
+            y += noise * philox_normal((nb, sc), seed=seed * 1000003 + int(eng.gids[k0]),
+                                       stream_id=100000 + c0 // s_chunk, dtype=torch.float32,
+                                       device=dev)
+            LA.gram_tc(X, dp, out=G, accumulate=True)
+            b[:, :d] += torch.einsum("nsd,ns->nd", X, y).double()
+            hyy += 0.5 * (y.double() ** 2).sum(1)
+            del X, y
+        Gsum += G.sum(0)
+        bsum += b.sum(0)
+        hsum += hyy.sum()
+        eng.ingest_gram(G, b, hyy, k0)
+        del G
+        if verbose and eng.dist.rank == 0:
+            print(f"  setup(tc): workers {k0 + nb}/{eng.Nloc}", flush=True)
     eng.dist.all_reduce_sum_(Gsum)
     eng.dist.all_reduce_sum_(bsum)
     eng.dist.all_reduce_sum_(hsum)
