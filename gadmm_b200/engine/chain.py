@@ -273,7 +273,7 @@ class ChainEngine:
         (dynamic_group_ADMM_closedForm.m:18-21).  Returns ``Iter``."""
         num_iter = self.max_iter if num_iter is None else min(int(num_iter), self.max_iter)
         nv.lib().gadmm_chain_configure()
-        done = 0
+        done = getattr(self, "_resume_from", 0)
         while done < num_iter:
             it_next = done + 1
             if rechain is not None and coherence is not None and it_next > 1 \
@@ -328,21 +328,60 @@ class ChainEngine:
         obj = self.obj_hist[1:Iter + 1].cpu().numpy().copy()
         loss = self.loss_hist[1:Iter + 1].cpu().numpy().copy()
         t = self.t_hist[1:Iter + 1].to(torch.float64)
-        tv = (t - t[0]) * 1e-9 if Iter > 0 else t
+        if Iter > 0:
+            live = t > 0                       # resumed runs carry no clock for restored iterations
+            t0 = t[live][0] if bool(live.any()) else t[0]
+            tv = torch.clamp((t - t0) * 1e-9, min=0.0)
+        else:
+            tv = t
         if self.dist.world > 1:
             import torch.distributed as dist
             dist.all_reduce(tv, op=dist.ReduceOp.MAX)
         return obj, loss, Iter, tv.cpu().numpy()
 
     def state(self):
-        """Checkpointable solver state: theta, duals, iteration, path."""
+        """Checkpointable solver state: theta and node duals of *all*
+        workers (d x N, gathered over the ranks), iteration, chain, curves so far.  Identical on
+        every rank; ``np.savez`` / ``scipy.io.savemat`` friendly."""
         torch.cuda.synchronize(self.dev)
         it = int(self.ctrl[0].item()) - 1
         slot = it & 1
-        th_loc = self.theta[slot, torch.from_numpy(self.gids).long().to(self.dev), :self.d]
-        return {"theta_local": th_loc.cpu().numpy().T.copy(), "dual_local": self.nu[:, :self.d].cpu().numpy().T.copy(),
-                "gids": self.gids.copy(), "iteration": it,
-                "path": None if self.path0 is None else self.path0 + 1}
+        idx = torch.from_numpy(self.gids).long().to(self.dev)
+        th = torch.zeros((self.N, self.d), dtype=torch.float64, device=self.dev)
+        nu = torch.zeros((self.N, self.d), dtype=torch.float64, device=self.dev)
+        th[idx] = self.theta[slot, idx, :self.d]
+        nu[idx] = self.nu[:, :self.d]
+        self.dist.all_reduce_sum_(th)
+        self.dist.all_reduce_sum_(nu)
+        return {"theta": th.cpu().numpy().T.copy(), "dual": nu.cpu().numpy().T.copy(),
+                "iteration": it, "path": None if self.path0 is None else self.path0 + 1,
+                "obj": self.obj_hist[1:it + 1].cpu().numpy().copy(),
+                "loss": self.loss_hist[1:it + 1].cpu().numpy().copy(),
+                "rho": self.rho}
+
+    def load_state(self, st):
+        """Resume from :meth:`state` (or from an oracle ``return_state`` dict of a node-dual run):
+        the next iteration to run is ``st['iteration'] + 1``."""
+        it = int(st["iteration"])
+        th = torch.as_tensor(np.asarray(st["theta"], dtype=np.float64).T.copy(), device=self.dev)
+        nu = torch.as_tensor(np.asarray(st["dual"], dtype=np.float64).T.copy(), device=self.dev)
+        idx = torch.from_numpy(self.gids).long().to(self.dev)
+        self.theta.zero_()
+        self.theta[:, :, :self.d] = th.unsqueeze(0)
+        self.nu.zero_()
+        self.nu[:, :self.d] = nu[idx]
+        self.flags.fill_(it)
+        self.objflag.zero_()
+        n = min(it, len(st.get("obj", [])))
+        if n:
+            self.obj_hist[1:n + 1] = torch.as_tensor(np.asarray(st["obj"][:n]), device=self.dev)
+            self.loss_hist[1:n + 1] = torch.as_tensor(np.asarray(st["loss"][:n]), device=self.dev)
+        self.ctrl[0] = it + 1
+        self.ctrl[1] = 0
+        self._resume_from = it
+        if st.get("path") is not None and self.path0 is None:
+            self.set_path(np.asarray(st["path"], dtype=np.int64) - 1)
+        self.dist.barrier()
 
 
 def nv_cudart_memcpy(dst_ptr: int, src_ptr: int, nbytes: int):

@@ -25,14 +25,19 @@ def _energy(cost_of_iter, Iter):
 
 
 def gadmm_closed_form(XX, YY, rho, no_workers, num_feature, noSamples, num_iter, obj0, acc,
-                      store="f64", window=32, dist=None, theta0=None, return_engine=False):
+                      store="f64", window=32, dist=None, theta0=None, return_engine=False,
+                      state=None, return_state=False):
     """``group_ADMM_closedForm`` on the GPU.  Node-dual form internally; the iterates equal the
     edge-dual ones (nu_n = lambda_n - lambda_{n-1})."""
     eng = _engine(XX, YY, rho, no_workers, num_feature, noSamples, num_iter, obj0, acc, False,
                   store, dist, theta0)
     eng.set_path(np.arange(no_workers))
+    if state is not None:
+        eng.load_state(state)
     it = eng.run(num_iter, window=window)
     res = eng.results(it)
+    if return_state:
+        res = res + (eng.state(),)
     return res + (eng,) if return_engine else res
 
 

@@ -95,3 +95,21 @@ def test_opt_sol_on_gpu(small_linear):
     p = small_linear
     assert g.opt_sol_closedForm(p["XX"], p["YY"], backend="b200") == pytest.approx(
         O.opt_sol_closedForm(p["XX"], p["YY"]), rel=1e-9, abs=1e-9)
+
+
+def test_checkpoint_resume_matches_uninterrupted_run(small_linear):
+    """state_out after 40 iterations -> state_in: the resumed curve continues bit-for-bit."""
+    p = small_linear
+    obj0 = O.opt_sol_closedForm(p["XX"], p["YY"])
+    args = (p["XX"], p["YY"], 2.0, p["N"], p["d"], p["s"])
+    full = g.group_ADMM_closedForm(*args, 120, obj0, 0.0, backend="b200")
+    part = g.group_ADMM_closedForm(*args, 40, obj0, 0.0, backend="b200", return_state=True)
+    st = part[4]
+    assert st["iteration"] == 40 and st["theta"].shape == (p["d"], p["N"])
+    rest = g.group_ADMM_closedForm(*args, 120, obj0, 0.0, backend="b200", state=st)
+    assert rest[2] == 120
+    np.testing.assert_array_equal(rest[0], full[0])
+    # the node duals of the oracle's node-dual run are interchangeable with the engine's
+    o = O.static_group_ADMM_closedForm(*args, 40, obj0, 0.0, 10 ** 9, np.ones((1, p["N"] - 1)),
+                                       return_state=True)
+    np.testing.assert_allclose(o[5]["dual"], st["dual"], rtol=1e-9, atol=1e-12)
