@@ -16,6 +16,15 @@
 
 namespace gadmm {
 
+__device__ __forceinline__ double mm_ld_reduce_add(const double* mc) {
+  double v;   // in-switch (NVLS) sum of the same offset on every GPU; SASS: LDGMC.E.ADD.F64
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.f64 %0, [%1];" : "=d"(v) : "l"(mc) : "memory");
+  return v;
+}
+__device__ __forceinline__ void mm_st(double* mc, double v) {   // broadcast store to every GPU
+  asm volatile("multimem.st.relaxed.sys.global.f64 [%0], %1;" ::"l"(mc), "d"(v) : "memory");
+}
+
 constexpr int kUPad = 64;   // ubuf row = dp + kUPad doubles; [dp] carries the objective partial
 
 struct StarWorkerX {
@@ -76,17 +85,29 @@ star_workers_kernel(const GadmmStar p) {
   if (gticket != (unsigned)(p.Nw - 1)) return;
   __threadfence();
   const size_t row = (size_t)dp + kUPad;
-  const size_t slot = ((size_t)(it & 1ull) * p.nranks + p.rank) * row;
   double fpart = 0.0;
   for (int i = threadIdx.x; i < p.Nw; i += blockDim.x) fpart += __ldcg(p.fw + i);
   fpart = block_sum(fpart, red);
-  for (int j = threadIdx.x; j < dp; j += blockDim.x) {
-    double u = 0.0;
-    for (int i = 0; i < p.Nw; ++i) u += __ldcg(p.U + (size_t)i * dp + j);
-    for (int q = 0; q < p.nranks; ++q) p.ubuf_peer[q][slot + j] = u;
+  if (p.nvls) {
+    // NVLS mode: the partial stays in this GPU's buffer (same offset on every GPU); the server
+    // sums all of them with one multimem.ld_reduce per element.
+    double* mine = p.ubuf + (size_t)(it & 1ull) * p.nranks * row;
+    for (int j = threadIdx.x; j < dp; j += blockDim.x) {
+      double u = 0.0;
+      for (int i = 0; i < p.Nw; ++i) u += __ldcg(p.U + (size_t)i * dp + j);
+      mine[j] = u;
+    }
+    if (threadIdx.x == 0) mine[dp] = fpart;
+  } else {
+    const size_t slot = ((size_t)(it & 1ull) * p.nranks + p.rank) * row;
+    for (int j = threadIdx.x; j < dp; j += blockDim.x) {
+      double u = 0.0;
+      for (int i = 0; i < p.Nw; ++i) u += __ldcg(p.U + (size_t)i * dp + j);
+      for (int q = 0; q < p.nranks; ++q) p.ubuf_peer[q][slot + j] = u;
+    }
+    if (threadIdx.x == 0)
+      for (int q = 0; q < p.nranks; ++q) p.ubuf_peer[q][slot + dp] = fpart;
   }
-  if (threadIdx.x == 0)
-    for (int q = 0; q < p.nranks; ++q) p.ubuf_peer[q][slot + dp] = fpart;
   __syncthreads();
   if (threadIdx.x == 0) {
     p.counters[p.Nw] = 0u;
@@ -99,13 +120,16 @@ star_workers_kernel(const GadmmStar p) {
 struct StarServerX {
   const double* bs;
   const double* ubuf;   // this iteration's slot base: [nranks][dp + kUPad]
+  const double* mc;     // multicast alias of the slot base (NVLS mode) or null
   int nranks;
   size_t row;
-  __device__ __forceinline__ double operator()(int j) const {
+  __device__ __forceinline__ double usum(int j) const {
+    if (mc) return mm_ld_reduce_add(mc + j);
     double u = 0.0;
     for (int q = 0; q < nranks; ++q) u += __ldcg(ubuf + q * row + j);   // fixed rank order
-    return bs[j] + u;
+    return u;
   }
+  __device__ __forceinline__ double operator()(int j) const { return bs[j] + usum(j); }
 };
 
 template <typename T>
@@ -121,8 +145,24 @@ star_server_kernel(const GadmmStar p) {
     for (int q = 0; q < p.nranks; ++q) wait_flag_ge(p.uflag + (it & 1ull) * p.nranks + q, it);
   __syncthreads();
   const size_t row = (size_t)dp + kUPad;
-  const double* ub = p.ubuf + (size_t)(it & 1ull) * p.nranks * row;
-  StarServerX xf{p.bs, ub, p.nranks, row};
+  const size_t slot_off = (size_t)(it & 1ull) * p.nranks * row;
+  const double* ub = p.ubuf + slot_off;
+  if (p.nvls && p.rank != p.server_rank) {
+    // NVLS mode, non-server GPU: z and the objective arrive by multicast store from the server
+    if (blockIdx.x != 0) return;
+    if (threadIdx.x == 0) {
+      wait_flag_ge(p.zflag, it);
+      const double total = *reinterpret_cast<volatile double*>(p.zobj + (it & 3ull));
+      const double loss = fabs(total - p.obj0);
+      p.obj_hist[it] = total;
+      p.loss_hist[it] = loss;
+      p.t_hist[it] = globaltimer_ns();
+      if (loss < p.acc && p.ctrl[1] == 0ull) p.ctrl[1] = it;
+      p.ctrl[0] = it + 1ull;
+    }
+    return;
+  }
+  StarServerX xf{p.bs, ub, p.nvls ? p.ubuf_mc + slot_off : nullptr, p.nranks, row};
   double* rowpart = p.rowpart + (size_t)p.Nw * dp;
   double* colpart = p.colpart + (size_t)p.Nw * colpart_elems(dp);
   const bool last = symv_cta<T>(sm, reinterpret_cast<const T*>(p.Ms), nT, blockIdx.x, xf, rowpart,
@@ -133,7 +173,7 @@ star_server_kernel(const GadmmStar p) {
   for (int j = threadIdx.x; j < dp; j += blockDim.x) {
     const double zn = symv_gather(rowpart, colpart, nT, j);
     const double r = xf(j);
-    p.z[j] = zn;
+    if (p.nvls) mm_st(p.z_mc + j, zn); else p.z[j] = zn;    // NVLS: broadcast z to every GPU
     s1 = fma(zn, r - crho * zn, s1);
     s2 = fma(p.bs[j], zn, s2);
   }
@@ -142,11 +182,18 @@ star_server_kernel(const GadmmStar p) {
   s2 = block_sum(s2, red);
   if (threadIdx.x == 0) {
     double total = 0.5 * s1 - s2 + p.hyy_s;
-    for (int q = 0; q < p.nranks; ++q) total += __ldcg(ub + q * row + dp);
+    if (p.nvls) total += mm_ld_reduce_add(p.ubuf_mc + slot_off + dp);
+    else for (int q = 0; q < p.nranks; ++q) total += __ldcg(ub + q * row + dp);
     const double loss = fabs(total - p.obj0);
     p.obj_hist[it] = total;
     p.loss_hist[it] = loss;
     p.t_hist[it] = globaltimer_ns();
+    if (p.nvls) {
+      mm_st(p.zobj_mc + (it & 3ull), total);
+      __threadfence_system();
+      for (int q = 0; q < p.nranks; ++q)
+        if (q != p.rank) st_release_sys(p.zflag_peer[q], it);
+    }
     if (loss < p.acc && p.ctrl[1] == 0ull) p.ctrl[1] = it;
     p.ctrl[0] = it + 1ull;
   }

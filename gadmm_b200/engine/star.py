@@ -18,7 +18,8 @@ from ..parallel.runtime import Dist, partition
 
 
 class StarEngine:
-    def __init__(self, XX, YY, rho, N, d, s, max_iter, obj0, acc, dist=None, store="f64", stop=True):
+    def __init__(self, XX, YY, rho, N, d, s, max_iter, obj0, acc, dist=None, store="f64", stop=True,
+                 nvls="auto"):
         self.dist = dist or Dist()
         D = self.dist
         dev = self.dev = D.device
@@ -48,18 +49,31 @@ class StarEngine:
         self.bs, self.hyy_s = bs[0].contiguous(), float(hs[0].item())
         self.lam = torch.zeros((Nw, dp), dtype=f64, device=dev)
         self.theta = torch.zeros((Nw, dp), dtype=f64, device=dev)
-        self.z = torch.zeros((dp,), dtype=f64, device=dev)
         self.U = torch.zeros((Nw, dp), dtype=f64, device=dev)
         self.fw = torch.zeros((Nw,), dtype=f64, device=dev)
         W = D.world
         row = dp + 64
+        # symmetric region: ubuf[2][W][row] | uflag[2][W] | z[dp] | zobj[4] | zflag[1]
         sz_u = 2 * W * row * 8
-        self._sym = D.symm_bytes(sz_u + 2 * W * 8)
-        self.ubuf = self._sym.local[:sz_u].view(f64)
-        self.uflag = self._sym.local[sz_u:sz_u + 2 * W * 8].view(torch.int64)
-        self.ubuf_peer = torch.tensor(self._sym.peer_ptrs, dtype=torch.int64, device=dev)
-        self.uflag_peer = torch.tensor([q + sz_u for q in self._sym.peer_ptrs], dtype=torch.int64,
-                                       device=dev)
+        off_flag = sz_u
+        off_z = off_flag + (2 * W * 8 + 255) // 256 * 256
+        off_zobj = off_z + dp * 8
+        off_zflag = off_zobj + 256
+        self._sym = D.symm_bytes(off_zflag + 256)
+        loc = self._sym.local
+        self.ubuf = loc[:sz_u].view(f64)
+        self.uflag = loc[off_flag:off_flag + 2 * W * 8].view(torch.int64)
+        self.z = loc[off_z:off_z + dp * 8].view(f64)
+        self.zobj = loc[off_zobj:off_zobj + 32].view(f64)
+        self.zflag = loc[off_zflag:off_zflag + 8].view(torch.int64)
+        peers = self._sym.peer_ptrs
+        self.ubuf_peer = torch.tensor(peers, dtype=torch.int64, device=dev)
+        self.uflag_peer = torch.tensor([q + off_flag for q in peers], dtype=torch.int64, device=dev)
+        self.zflag_peer = torch.tensor([q + off_zflag for q in peers], dtype=torch.int64, device=dev)
+        mc = self._sym.mc_ptr
+        self.nvls = bool(W > 1 and mc and nvls in ("auto", True))
+        if nvls is True and W > 1 and not mc:
+            raise RuntimeError("NVLS multicast is not available for this process group")
         cpe = max(1, (dp // 64) * (dp // 64 - 1) // 2 * 64)
         self.rowpart = torch.empty((Nw + 1, dp), dtype=f64, device=dev)
         self.colpart = torch.empty((Nw + 1, cpe), dtype=f64, device=dev)
@@ -79,6 +93,9 @@ class StarEngine:
                                             self.counters.data_ptr())
         p.ctrl, p.obj_hist, p.loss_hist, p.t_hist = (self.ctrl.data_ptr(), self.obj_hist.data_ptr(),
                                                      self.loss_hist.data_ptr(), self.t_hist.data_ptr())
+        p.ubuf_mc, p.z_mc, p.zobj_mc = mc, mc + off_z, mc + off_zobj
+        p.zobj, p.zflag, p.zflag_peer = self.zobj.data_ptr(), self.zflag.data_ptr(), self.zflag_peer.data_ptr()
+        p.nvls, p.server_rank = int(self.nvls), 0
         p.rho, p.obj0, p.acc, p.hyy_s = self.rho, float(obj0), float(acc), self.hyy_s
         p.d, p.dp, p.N, p.Nw, p.rank, p.nranks = self.d, dp, self.N, Nw, D.rank, D.world
         p.store, p.max_iter = self.store, self.max_iter
@@ -129,9 +146,9 @@ class StarEngine:
 
 
 def star_admm(XX, YY, rho, no_workers, num_feature, noSamples, num_iter, obj0, acc, store="f64",
-              dist=None, window=64, return_engine=False):
+              dist=None, window=64, return_engine=False, nvls="auto"):
     eng = StarEngine(XX, YY, rho, no_workers, num_feature, noSamples, num_iter, obj0, acc, dist=dist,
-                     store=store)
+                     store=store, nvls=nvls)
     it = eng.run(num_iter, window=window)
     res = eng.results(it)
     return res + (eng,) if return_engine else res

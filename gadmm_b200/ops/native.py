@@ -126,9 +126,12 @@ class GadmmStar(C.Structure):
         ("theta", _vp), ("z", _vp), ("U", _vp), ("fw", _vp), ("ubuf", _vp), ("uflag", _vp),
         ("ubuf_peer", _vp), ("uflag_peer", _vp), ("rowpart", _vp), ("colpart", _vp),
         ("counters", _vp), ("ctrl", _vp), ("obj_hist", _vp), ("loss_hist", _vp), ("t_hist", _vp),
+        ("ubuf_mc", _vp), ("z_mc", _vp), ("zobj", _vp), ("zobj_mc", _vp), ("zflag", _vp),
+        ("zflag_peer", _vp),
         ("rho", C.c_double), ("obj0", C.c_double), ("acc", C.c_double), ("hyy_s", C.c_double),
         ("d", C.c_int), ("dp", C.c_int), ("N", C.c_int), ("Nw", C.c_int), ("rank", C.c_int),
-        ("nranks", C.c_int), ("store", C.c_int), ("max_iter", C.c_int),
+        ("nranks", C.c_int), ("store", C.c_int), ("max_iter", C.c_int), ("nvls", C.c_int),
+        ("server_rank", C.c_int),
     ]
 
 

@@ -55,6 +55,7 @@ class SymmBuffer:
     local: torch.Tensor          # uint8, this rank's buffer
     peer_ptrs: List[int]         # device pointer of the buffer on every rank (index = rank)
     handle: object = None
+    mc_ptr: int = 0              # NVLS multicast alias of the buffer (0 = no multicast support)
 
 
 class Dist:
@@ -85,7 +86,12 @@ class Dist:
         t.zero_()
         torch.cuda.synchronize(self.device)
         dist.barrier()
-        return SymmBuffer(t, [int(p) for p in hdl.buffer_ptrs], hdl)
+        mc = 0
+        try:
+            mc = int(hdl.multicast_ptr or 0)
+        except Exception:
+            mc = 0
+        return SymmBuffer(t, [int(p) for p in hdl.buffer_ptrs], hdl, mc)
 
     def barrier(self):
         if self.world > 1:

@@ -207,8 +207,17 @@ typedef struct GadmmStar {
   double* obj_hist;
   double* loss_hist;
   unsigned long long* t_hist;
+  /* NVLS mode (nvls != 0): partial sums stay local and are reduced in the NVSwitch with
+   * multimem.ld_reduce by the server GPU only, which multicasts z and the objective back
+   * (multimem.st) and raises zflag on every other GPU. */
+  const double* ubuf_mc;     /* multicast alias of ubuf */
+  double* z_mc;              /* multicast alias of z (z must then live in symmetric memory) */
+  double* zobj;              /* symmetric: [4] objective broadcast ring */
+  double* zobj_mc;
+  unsigned long long* zflag; /* symmetric: [1] */
+  unsigned long long* const* zflag_peer; /* [nranks] */
   double rho, obj0, acc, hyy_s;
-  int d, dp, N, Nw, rank, nranks, store, max_iter;
+  int d, dp, N, Nw, rank, nranks, store, max_iter, nvls, server_rank;
 } GadmmStar;
 int gadmm_star_iterate(const GadmmStar* p, int n_iter, void* stream);
 

@@ -43,8 +43,18 @@ def main():
     c = g.group_ADMM_closedForm(XX, YY, 1.5, N, d, s, 3000, obj0, 0.0, backend="b200", dist=D)
     r = O.group_ADMM_closedForm(XX, YY, 1.5, N, d, s, 3000, obj0, 0.0)
     np.testing.assert_allclose(c[0], r[0], rtol=1e-9, atol=1e-9)
+    # star ADMM: in-kernel reduction by P2P stores, and by NVLS multimem.ld_reduce / multimem.st
+    from gadmm_b200.engine.star import star_admm
+    rs = O.standared_ADMM(XX, YY, 1.0, N, d, s, 500, obj0, 1e-6)
+    used = []
+    for mode in (False, "auto"):
+        out = star_admm(XX, YY, 1.0, N, d, s, 500, obj0, 1e-6, dist=D, nvls=mode, return_engine=True)
+        assert out[2] == rs[2], (mode, out[2], rs[2])
+        np.testing.assert_allclose(out[0], rs[0], rtol=1e-9, atol=1e-9)
+        used.append(out[4].nvls)
     D.barrier()
     if D.rank == 0:
+        print(f"STAR_NVLS_USED={used}")
         print(f"MULTIGPU_OK world={D.world}")
     torch.distributed.destroy_process_group()
 
