@@ -84,13 +84,17 @@ gadmm_half_iter_kernel(const GadmmChain c, const int color) {
   if (c.ctrl[2] != 0ull && c.ctrl[1] != 0ull) return;   // converged: freeze the state
   if (it > (unsigned long long)c.max_iter) return;
 
+  // let the next phase's grid start filling SMs as soon as every CTA of this one is resident
+  if (c.pdl) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   const int g = c.gid[k], l = c.left[k], r = c.right[k];
   // heads read the tails' previous iterate, tails read this iteration's heads
   const unsigned long long need = (color == 0) ? it - 1 : it;
   const size_t slot_in = (size_t)(need & 1ull) * c.Nglob;
   if (threadIdx.x == kConsumerWarps * 32) {   // producer lane 0 waits for remote neighbours
-    if (l >= 0 && c.owner[l] != c.rank) wait_flag_ge(c.flags + l, need);
-    if (r >= 0 && c.owner[r] != c.rank) wait_flag_ge(c.flags + r, need);
+    // With programmatic dependent launch the previous phase may still be running on this GPU,
+    // so local neighbours are awaited through the same version flags as remote ones.
+    if (l >= 0 && (c.pdl || c.owner[l] != c.rank)) wait_flag_ge(c.flags + l, need);
+    if (r >= 0 && (c.pdl || c.owner[r] != c.rank)) wait_flag_ge(c.flags + r, need);
   }
   __syncthreads();
 
@@ -132,7 +136,7 @@ gadmm_half_iter_kernel(const GadmmChain c, const int color) {
     __threadfence_system();
     if (p0 >= 0) st_release_sys(c.flags_peer[p0] + g, it);
     if (p1 >= 0) st_release_sys(c.flags_peer[p1] + g, it);
-    c.flags[g] = it;
+    st_release_sys(c.flags + g, it);
   }
 }
 
@@ -147,8 +151,9 @@ gadmm_dual_objective_kernel(const GadmmChain c) {
   const int k = blockIdx.x;
   const int g = c.gid[k], l = c.left[k], r = c.right[k];
   if (threadIdx.x == 0) {
-    if (l >= 0 && c.owner[l] != c.rank) wait_flag_ge(c.flags + l, it);
-    if (r >= 0 && c.owner[r] != c.rank) wait_flag_ge(c.flags + r, it);
+    if (c.pdl) wait_flag_ge(c.flags + g, it);          // own finisher (tail phase may be running)
+    if (l >= 0 && (c.pdl || c.owner[l] != c.rank)) wait_flag_ge(c.flags + l, it);
+    if (r >= 0 && (c.pdl || c.owner[r] != c.rank)) wait_flag_ge(c.flags + r, it);
   }
   __syncthreads();
   const size_t slot = (size_t)(it & 1ull) * c.Nglob;
@@ -216,7 +221,22 @@ static int launch_half(const GadmmChain* c, int color, cudaStream_t st) {
     configured = true;
   }
   const int nT = c->dp / kT, npairs = (nT + 1) / 2;
-  gadmm_half_iter_kernel<T><<<c->Nloc * npairs, kSymvThreads, smem, st>>>(*c, color);
+  if (c->pdl && color == 1) {
+    // tail phase: programmatic dependent launch behind the head phase (ordering by flags)
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(c->Nloc * npairs);
+    cfg.blockDim = dim3(kSymvThreads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    GADMM_CUDA_OK(cudaLaunchKernelEx(&cfg, gadmm_half_iter_kernel<T>, *c, color));
+  } else {
+    gadmm_half_iter_kernel<T><<<c->Nloc * npairs, kSymvThreads, smem, st>>>(*c, color);
+  }
   GADMM_CUDA_OK(cudaGetLastError());
   return 0;
 }
@@ -271,7 +291,21 @@ int gadmm_chain_half_iter(const GadmmChain* c, int color, void* stream) {
 
 int gadmm_chain_dual_objective(const GadmmChain* c, void* stream) {
   GADMM_REQUIRE(c && c->Nloc > 0, "chain: every rank must own at least one worker");
-  gadmm_dual_objective_kernel<<<c->Nloc, 256, 0, (cudaStream_t)stream>>>(*c);
+  if (c->pdl) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(c->Nloc);
+    cfg.blockDim = dim3(256);
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = (cudaStream_t)stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    GADMM_CUDA_OK(cudaLaunchKernelEx(&cfg, gadmm_dual_objective_kernel, *c));
+  } else {
+    gadmm_dual_objective_kernel<<<c->Nloc, 256, 0, (cudaStream_t)stream>>>(*c);
+  }
   GADMM_CUDA_OK(cudaGetLastError());
   return 0;
 }

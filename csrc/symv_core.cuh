@@ -171,7 +171,8 @@ __device__ __forceinline__ double symv_gather(const double* rowpart, const doubl
                                               int j) {
   const int J = j / kT, jj = j % kT;
   double v = __ldcg(rowpart + j);
-  for (int I = J + 1; I < nT; ++I) v += __ldcg(colpart + colpart_off(I, J) + jj);
+#pragma unroll 8
+  for (int I = J + 1; I < nT; ++I) v += __ldcg(colpart + colpart_off(I, J) + jj);   // loads overlap
   return v;
 }
 

@@ -17,6 +17,7 @@ static_group_ADMM_closedForm.m:19-160, dynamic_group_ADMM_closedForm.m:14-190.
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import Optional
 
 import numpy as np
@@ -35,7 +36,7 @@ def _carve(buf: torch.Tensor, off: int, nbytes: int, dtype) -> torch.Tensor:
 class ChainEngine:
     def __init__(self, N: int, d: int, rho: float, obj0: float, acc: float, max_iter: int,
                  dist: Optional[Dist] = None, store: str = "f64", dynamic: bool = False,
-                 stop: bool = True):
+                 stop: bool = True, pdl: bool = True):
         self.dist = dist or Dist()
         self.dev = self.dist.device
         self.N, self.d, self.rho = int(N), int(d), float(rho)
@@ -44,6 +45,7 @@ class ChainEngine:
         self.store = nv.STORE_F64 if store in ("f64", "fp64", nv.STORE_F64) else nv.STORE_F32
         self.dynamic = dynamic
         self.stop = stop
+        self.pdl = bool(pdl) and os.environ.get("GADMM_B200_NO_PDL") != "1"
         self.owner_np = partition(self.N, self.dist.world)
         self.gids = np.nonzero(self.owner_np == self.dist.rank)[0].astype(np.int32)
         self.Nloc = int(self.gids.shape[0])
@@ -245,6 +247,7 @@ class ChainEngine:
         c.rho, c.obj0, c.acc = self.rho, self.obj0, self.acc
         c.d, c.dp, c.Nglob, c.Nloc = self.d, self.dp, self.N, self.Nloc
         c.rank, c.nranks, c.store, c.max_iter = self.dist.rank, self.dist.world, self.store, self.max_iter
+        c.pdl = int(self.pdl)
         self._desc = c
         return c
 

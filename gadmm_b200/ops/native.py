@@ -34,7 +34,8 @@ class GadmmChain(C.Structure):
         ("obj_hist", _vp), ("loss_hist", _vp), ("t_hist", _vp),
         ("rho", C.c_double), ("obj0", C.c_double), ("acc", C.c_double),
         ("d", C.c_int), ("dp", C.c_int), ("Nglob", C.c_int), ("Nloc", C.c_int), ("rank", C.c_int),
-        ("nranks", C.c_int), ("store", C.c_int), ("max_iter", C.c_int),
+        ("nranks", C.c_int), ("store", C.c_int), ("max_iter", C.c_int), ("pdl", C.c_int),
+        ("reserved", C.c_int),
     ]
 
 

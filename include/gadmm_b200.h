@@ -110,6 +110,9 @@ typedef struct GadmmChain {
   double obj0;
   double acc;
   int d, dp, Nglob, Nloc, rank, nranks, store, max_iter;
+  int pdl;                   /* 1: tail and dual kernels use programmatic dependent launch; phase
+                                ordering on one GPU then also goes through the version flags */
+  int reserved;
 } GadmmChain;
 
 int gadmm_chain_half_iter(const GadmmChain* c, int color, void* stream);
