@@ -81,23 +81,49 @@ __device__ bool symv_cta(SymvSmem<T>& sm, const T* __restrict__ S, int nT, int p
 
   if (warp == kConsumerWarps) {
     // ------------------------------------------------------------------ producer warp
+    // The x slices are fetched kXG tiles ahead in registers (group g+1 is in flight while the
+    // tiles of group g are issued), so the global-load latency of the fused RHS assembly never
+    // sits between two bulk copies -- that matters when a GPU has few CTAs in flight (one worker
+    // per GPU: 128 CTAs, each needing ~50 GB/s).
+    constexpr int kXG = 4;
     int stage = 0;
     uint32_t phase = 0;
     for (int rr = 0; rr < nrows; ++rr) {
       const int I = rr == 0 ? rowA : rowB;
+      double cur[2 * kXG], nxt[2 * kXG];
+#pragma unroll
+      for (int q = 0; q < kXG; ++q) {
+        const bool ok = q <= I;
+        nxt[2 * q] = ok ? xf(q * kT + lane) : 0.0;
+        nxt[2 * q + 1] = ok ? xf(q * kT + lane + 32) : 0.0;
+      }
       // x_I slice for the column products of this tile-row
       sm.xrow[rr][lane] = xf(I * kT + lane);
       sm.xrow[rr][lane + 32] = xf(I * kT + lane + 32);
       const T* rowbase = S + ((size_t)I * (I + 1) / 2) * (kT * kT);
-      for (int J = 0; J <= I; ++J) {
-        mbar_wait(&sm.empty[stage], phase ^ 1);
-        if (lane == 0) bulk_g2s(sm.tile[stage], rowbase + (size_t)J * (kT * kT), kTileBytes,
-                                &sm.full[stage]);
-        sm.xs[stage][lane] = xf(J * kT + lane);
-        sm.xs[stage][lane + 32] = xf(J * kT + lane + 32);
-        __syncwarp();
-        if (lane == 0) mbar_arrive_expect_tx(&sm.full[stage], kTileBytes);
-        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      for (int J0 = 0; J0 <= I; J0 += kXG) {
+#pragma unroll
+        for (int q = 0; q < 2 * kXG; ++q) cur[q] = nxt[q];
+#pragma unroll
+        for (int q = 0; q < kXG; ++q) {            // prefetch the next group's slices
+          const int Jn = J0 + kXG + q;
+          const bool ok = Jn <= I;
+          nxt[2 * q] = ok ? xf(Jn * kT + lane) : 0.0;
+          nxt[2 * q + 1] = ok ? xf(Jn * kT + lane + 32) : 0.0;
+        }
+#pragma unroll
+        for (int q = 0; q < kXG; ++q) {
+          const int J = J0 + q;
+          if (J > I) break;
+          mbar_wait(&sm.empty[stage], phase ^ 1);
+          if (lane == 0) bulk_g2s(sm.tile[stage], rowbase + (size_t)J * (kT * kT), kTileBytes,
+                                  &sm.full[stage]);
+          sm.xs[stage][lane] = cur[2 * q];
+          sm.xs[stage][lane + 32] = cur[2 * q + 1];
+          __syncwarp();
+          if (lane == 0) mbar_arrive_expect_tx(&sm.full[stage], kTileBytes);
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
       }
     }
   } else {

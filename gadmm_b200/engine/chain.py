@@ -295,6 +295,81 @@ class ChainEngine:
                     return hit
         return num_iter
 
+    # ------------------------------------------------------- D-GADMM with device-side re-chaining
+    def run_device_rechain(self, num_iter, chain_source, tau, window: int = 32, chunk: int = 256):
+        """D-GADMM without the host in the loop: the chains of the coming windows are uploaded in
+        chunks of ``chunk`` rows; two tiny kernels in front of every head kernel switch tables and
+        pull the new remote neighbours' theta over NVLink when ``it % tau == 0`` (csrc/rechain.cu).
+        ``chain_source(kk)`` returns the 0-based chain of window ``kk`` (kk = 1, 2, ...; called in
+        increasing order).  Returns ``Iter``."""
+        assert self.dynamic, "device re-chaining needs both inverses (dynamic=True)"
+        num_iter = min(int(num_iter), self.max_iter)
+        L = nv.lib()
+        L.gadmm_chain_configure()
+        N, dev = self.N, self.dev
+        tau_i = 0 if tau >= 1e8 else int(tau)
+        K = int(chunk)
+        paths_dev = torch.zeros((K, N), dtype=torch.int32, device=dev)
+        paths_host = torch.zeros((K, N), dtype=torch.int32).pin_memory()
+        pos = torch.zeros((N,), dtype=torch.int32, device=dev)
+        dyn = torch.zeros((2,), dtype=torch.int64, device=dev)
+        dyn_host = torch.zeros((2,), dtype=torch.int64).pin_memory()
+        r = nv.GadmmRechain()
+        r.paths, r.pos, r.tab, r.Mptr = paths_dev.data_ptr(), pos.data_ptr(), self.tab.data_ptr(), self.Mptr.data_ptr()
+        r.owner, r.theta, r.flags = self.owner.data_ptr(), self.theta.data_ptr(), self.flags.data_ptr()
+        r.theta_peer, r.ctrl, r.dyn = self.theta_peer.data_ptr(), self.ctrl.data_ptr(), dyn.data_ptr()
+        r.base_c1, r.base_c2 = self.P[1].data_ptr(), self.P[2].data_ptr()
+        r.stride_bytes = self.P[2].stride(0) * self.P[2].element_size()
+        r.tau, r.N, r.Nloc, r.dp = tau_i, N, self.Nloc, self.dp
+        r.rank, r.nranks, r.K = self.dist.rank, self.dist.world, K
+        c = self.desc()
+        graphs = {}
+
+        def launch(n):
+            for _ in range(n):
+                nv.check(L.gadmm_rechain(C.byref(r), nv.stream_ptr()))
+                nv.check(L.gadmm_chain_iterate(C.byref(c), 1, nv.stream_ptr()))
+
+        def iterate(n):
+            if n >= 4:
+                g = graphs.get(n)
+                if g is None:
+                    torch.cuda.synchronize(dev)
+                    g = torch.cuda.CUDAGraph()
+                    with torch.cuda.graph(g):
+                        launch(n)
+                    graphs[n] = g
+                g.replay()
+            else:
+                launch(n)
+            self.launches += 5 * n
+
+        done, base = 0, 1
+        while done < num_iter:
+            if tau_i:
+                torch.cuda.current_stream().synchronize()       # previous chunk fully consumed
+                for q in range(K):
+                    paths_host[q] = torch.from_numpy(np.asarray(chain_source(base + q), dtype=np.int32))
+                dyn_host[0], dyn_host[1] = base, K
+                paths_dev.copy_(paths_host, non_blocking=True)
+                dyn.copy_(dyn_host, non_blocking=True)
+                it_star = (base + K) * tau_i if tau_i > 1 else base + K + 1
+                target = min(num_iter, it_star - 1)
+            else:
+                target = num_iter
+            while done < target:
+                n = min(window, target - done)
+                iterate(n)
+                done += n
+                if self.stop:
+                    hit = int(self.ctrl[1].item())
+                    if hit:
+                        self._keep = (paths_dev, pos, dyn)
+                        return hit
+            base += K
+        self._keep = (paths_dev, pos, dyn)
+        return num_iter
+
     # ------------------------------------------------------------------- streaming public API
     def step(self, path0=None):
         """One GADMM iteration driven from the host, end to end: the step's control block (chain

@@ -62,19 +62,26 @@ def static_gadmm(XX, YY, rho, no_workers, num_feature, noSamples, num_iter, obj0
 
 
 def _dynamic(XX, YY, rho, N, d, s, num_iter, obj0, acc, first_path, first_cost, tau, next_chain,
-             store, window, dist, return_engine):
+             store, window, dist, return_engine, rechain_mode="device"):
+    """``rechain_mode="device"``: chains are uploaded in chunks and switched by the re-chain kernels
+    inside the CUDA graph (no host round trip per window); ``"host"``: tables are rebuilt on the host
+    at every re-chain (kept for comparison / debugging)."""
     eng = _engine(XX, YY, rho, N, d, s, num_iter, obj0, acc, True, store, dist)
     eng.set_path(np.asarray(first_path, dtype=np.int64) - 1)
     cost_at = {1: float(first_cost)}
-    cur = [float(first_cost)]
+    tau_i = None if tau >= 1e8 else int(tau)
 
     def rechain(i):
         p1, pc = next_chain(i)
-        cur[0] = float(np.sum(pc))
-        cost_at[i] = cur[0]
+        cost_at[i] = float(np.sum(pc))
         return np.asarray(p1, dtype=np.int64) - 1
 
-    it = eng.run(num_iter, window=window, rechain=rechain, coherence=tau)
+    if rechain_mode == "device":
+        def chain_source(kk):
+            return rechain(kk * tau_i if tau_i > 1 else kk + 1)
+        it = eng.run_device_rechain(num_iter, chain_source, tau, window=window)
+    else:
+        it = eng.run(num_iter, window=window, rechain=rechain, coherence=tau)
     obj, loss, it, tv = eng.results(it)
     per = np.empty(it)
     c = cost_at[1]
@@ -87,7 +94,7 @@ def _dynamic(XX, YY, rho, N, d, s, num_iter, obj0, acc, first_path, first_cost, 
 
 def dynamic_gadmm(XX, YY, rho, no_workers, num_feature, noSamples, num_iter, obj0, acc, path,
                   pathCost, coherence_Time, rng=None, rechain=None, store="f64", window=32,
-                  dist=None, return_engine=False):
+                  dist=None, return_engine=False, rechain_mode="device"):
     """D-GADMM with live ``findPath2`` re-chaining (dynamic_group_ADMM_closedForm.m:18-21).  Chains
     are drawn on rank 0 and broadcast so that every GPU installs the same tables."""
     dist = dist or Dist()
@@ -102,12 +109,12 @@ def dynamic_gadmm(XX, YY, rho, no_workers, num_feature, noSamples, num_iter, obj
 
     return _dynamic(XX, YY, rho, no_workers, num_feature, noSamples, num_iter, obj0, acc, path,
                     np.sum(pathCost), coherence_Time, next_chain, store, window, dist,
-                    return_engine)
+                    return_engine, rechain_mode)
 
 
 def dynamic_gadmm_v0(XX, YY, rho, no_workers, num_feature, noSamples, num_iter, obj0, acc,
                      path_matrix, pathCost_matrix, coherence_Time, faithful=True, store="f64",
-                     window=32, dist=None, return_engine=False):
+                     window=32, dist=None, return_engine=False, rechain_mode="device"):
     paths = np.atleast_2d(np.asarray(path_matrix, dtype=np.int64))
     costs = np.atleast_2d(np.asarray(pathCost_matrix, dtype=np.float64))
     kk = [0]
@@ -117,9 +124,14 @@ def dynamic_gadmm_v0(XX, YY, rho, no_workers, num_feature, noSamples, num_iter, 
         kk[0] += 1
         return paths[kk[0]], costs[kk[0]]
 
+    def next_chain_safe(i):
+        if kk[0] + 1 >= paths.shape[0]:          # chunk pre-fetch may look past the supplied table
+            return paths[-1], costs[-1]
+        return next_chain(i)
+
     return _dynamic(XX, YY, rho, no_workers, num_feature, noSamples, num_iter, obj0, acc,
-                    paths[0], first_cost, coherence_Time, next_chain, store, window, dist,
-                    return_engine)
+                    paths[0], first_cost, coherence_Time, next_chain_safe, store, window, dist,
+                    return_engine, rechain_mode)
 
 
 def opt_sol_closed_form(XX, YY, return_theta=False):

@@ -146,3 +146,15 @@ class GadmmLogistic(C.Structure):
         ("N", C.c_int), ("s", C.c_int), ("d", C.c_int), ("dp", C.c_int), ("max_iter", C.c_int),
         ("max_inner", C.c_int),
     ]
+
+
+class GadmmRechain(C.Structure):
+    """Mirror of ``struct GadmmRechain`` (include/gadmm_b200.h)."""
+    _fields_ = [
+        ("paths", _vp), ("pos", _vp), ("tab", _vp), ("Mptr", _vp), ("owner", _vp), ("theta", _vp),
+        ("flags", _vp), ("theta_peer", _vp), ("ctrl", _vp),
+        ("base_c1", C.c_longlong), ("base_c2", C.c_longlong), ("stride_bytes", C.c_longlong),
+        ("dyn", _vp), ("tau", C.c_longlong),
+        ("N", C.c_int), ("Nloc", C.c_int), ("dp", C.c_int), ("rank", C.c_int), ("nranks", C.c_int),
+        ("K", C.c_int),
+    ]

@@ -124,6 +124,26 @@ int gadmm_chain_configure(void);
 /* Number of kernel launches gadmm_chain_iterate issues per iteration. */
 int gadmm_chain_launches_per_iter(void);
 
+/* ---- D-GADMM re-chaining on the device (K10; dynamic_group_ADMM_closedForm.m:18-21) -----------
+ * Launched once per iteration in front of the head kernel; a no-op unless
+ * it > 1 && it % tau == 0.  Window index kk = it/tau - (tau==1) - dyn[0] selects paths[kk]. */
+typedef struct GadmmRechain {
+  const int* paths;          /* [K][N] chains (0-based worker ids in chain order) */
+  int* pos;                  /* [N] scratch */
+  int* tab;                  /* [7][Nloc] gid,left,right,color,cmul,push0,push1 (GadmmChain tables) */
+  long long* Mptr;           /* [Nloc] */
+  const int* owner;          /* [N] */
+  double* theta;             /* local replica [2][N][dp] */
+  unsigned long long* flags; /* [N] */
+  double* const* theta_peer; /* [nranks] */
+  const unsigned long long* ctrl;
+  long long base_c1, base_c2, stride_bytes;   /* packed inverses for c=1 / c=2, bytes per worker */
+  const long long* dyn;      /* device [2]: window index of paths[0], number of valid rows */
+  long long tau;
+  int N, Nloc, dp, rank, nranks, K;
+} GadmmRechain;
+int gadmm_rechain(const GadmmRechain* p, void* stream);
+
 /* ---- first-order baselines (K7, K8; GD_DGD_LAG.m, GD_DGD_LAG_logistic.m, dual_averaging*.m) ---- */
 /* Gradient providers.  Linear: Y[n] = S_n x_n - b_n, fw[n] = 0.5 x'S x - b'x + hyy[n]; x_stride
  * = 0 shares one iterate between all workers (parameter-server methods). */
