@@ -110,6 +110,14 @@ gadmm_half_iter_kernel(const GadmmChain c, const int color) {
   const bool last = symv_cta<T>(sm, reinterpret_cast<const T*>(c.Mptr[k]), nT, p, xf, rowpart,
                                 colpart, c.counters + k, npairs);
   if (!last) return;
+  if (c.split_finish) {
+    // the partial sums of worker k are complete: hand over to gadmm_finish_kernel (many CTAs)
+    if (threadIdx.x == 0) {
+      __threadfence();
+      st_release_sys(c.wready + k, it);
+    }
+    return;
+  }
 
   // ---------------------------------------------------------------- finisher (one CTA per worker)
   const size_t slot_out = (size_t)(it & 1ull) * c.Nglob;
@@ -133,6 +141,81 @@ gadmm_half_iter_kernel(const GadmmChain c, const int color) {
   s2 = block_sum(s2, red);
   if (threadIdx.x == 0) {
     c.objw[k] = 0.5 * s1 - s2 + c.hyy[k];
+    __threadfence_system();
+    if (p0 >= 0) st_release_sys(c.flags_peer[p0] + g, it);
+    if (p1 >= 0) st_release_sys(c.flags_peer[p1] + g, it);
+    st_release_sys(c.flags + g, it);
+  }
+}
+
+// ------------------------------------------------------------------ parallel finisher (large d)
+// For d >= 512 the column-partial reduction is worth spreading over many CTAs: one CTA of 64
+// threads per 64-entry block of theta_n.  It waits (ld.acquire) until the streaming kernel has
+// published worker k's partials, adds them in a fixed order, writes theta (local replica + NVLink
+// P2P stores into the neighbour GPUs), and the last block of the worker folds the per-block
+// objective pieces and releases the version flags.  Launched with programmatic dependent launch
+// right behind the streaming kernel, so its CTAs fill SM slots as that kernel drains.
+__global__ void __launch_bounds__(64)
+gadmm_finish_kernel(const GadmmChain c, const int color) {
+  __shared__ double red[8];
+  __shared__ unsigned int ticket;
+  const int J = blockIdx.x, k = blockIdx.y, tid = threadIdx.x;
+  if (c.color[k] != color) return;
+  const unsigned long long it = c.ctrl[0];
+  if (c.ctrl[2] != 0ull && c.ctrl[1] != 0ull) return;
+  if (it > (unsigned long long)c.max_iter) return;
+  if (c.pdl) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  const int nT = c.dp / kT;
+  const int g = c.gid[k], l = c.left[k], r = c.right[k];
+  const unsigned long long need = (color == 0) ? it - 1 : it;
+  const size_t slot_in = (size_t)(need & 1ull) * c.Nglob;
+  if (tid == 0) wait_flag_ge(c.wready + k, it);
+  __syncthreads();
+  ChainX xf;
+  xf.b = c.b + (size_t)k * c.dp;
+  xf.nu = c.nu + (size_t)k * c.dp;
+  xf.tl = l >= 0 ? c.theta + (slot_in + l) * c.dp : nullptr;
+  xf.tr = r >= 0 ? c.theta + (slot_in + r) * c.dp : nullptr;
+  xf.rho = c.rho;
+  const double* rowpart = c.rowpart + (size_t)k * c.dp;
+  const double* colpart = c.colpart + (size_t)k * colpart_elems(c.dp);
+  const size_t slot_out = (size_t)(it & 1ull) * c.Nglob;
+  const int p0 = c.push0[k], p1 = c.push1[k];
+  const int j = J * kT + tid;
+  const double th = symv_gather(rowpart, colpart, nT, j);
+  const double rj = xf(j);
+  c.theta[(slot_out + g) * c.dp + j] = th;
+  if (p0 >= 0) c.theta_peer[p0][(slot_out + g) * c.dp + j] = th;   // NVLink P2P stores
+  if (p1 >= 0) c.theta_peer[p1][(slot_out + g) * c.dp + j] = th;
+  const double crho = c.rho * (double)c.cmul[k];
+  double s1 = th * (rj - crho * th), s2 = xf.b[j] * th;
+  s1 = warp_sum(s1);
+  s2 = warp_sum(s2);
+  if ((tid & 31) == 0) { red[(tid >> 5) * 2] = s1; red[(tid >> 5) * 2 + 1] = s2; }
+  __syncthreads();
+  if (tid == 0) {
+    double* sb = c.sblk + ((size_t)k * nT + J) * 2;
+    sb[0] = red[0] + red[2];
+    sb[1] = red[1] + red[3];
+    __threadfence_system();                      // theta stores (local + peers) before the ticket
+    ticket = atomicAdd(c.fin_counters + k, 1u);
+  }
+  __syncthreads();
+  if (ticket != (unsigned)(nT - 1)) return;
+  __threadfence();
+  double a1 = 0.0, a2 = 0.0;
+  for (int q = tid; q < nT; q += 64) {           // fixed partition + fixed tree: deterministic
+    a1 += __ldcg(c.sblk + ((size_t)k * nT + q) * 2);
+    a2 += __ldcg(c.sblk + ((size_t)k * nT + q) * 2 + 1);
+  }
+  a1 = warp_sum(a1);
+  a2 = warp_sum(a2);
+  __syncthreads();
+  if ((tid & 31) == 0) { red[(tid >> 5) * 2] = a1; red[(tid >> 5) * 2 + 1] = a2; }
+  __syncthreads();
+  if (tid == 0) {
+    c.fin_counters[k] = 0u;
+    c.objw[k] = 0.5 * (red[0] + red[2]) - (red[1] + red[3]) + c.hyy[k];
     __threadfence_system();
     if (p0 >= 0) st_release_sys(c.flags_peer[p0] + g, it);
     if (p1 >= 0) st_release_sys(c.flags_peer[p1] + g, it);
@@ -238,6 +321,19 @@ static int launch_half(const GadmmChain* c, int color, cudaStream_t st) {
     gadmm_half_iter_kernel<T><<<c->Nloc * npairs, kSymvThreads, smem, st>>>(*c, color);
   }
   GADMM_CUDA_OK(cudaGetLastError());
+  if (c->split_finish) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(nT, c->Nloc);
+    cfg.blockDim = dim3(64);
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = c->pdl ? 1 : 0;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    GADMM_CUDA_OK(cudaLaunchKernelEx(&cfg, gadmm_finish_kernel, *c, color));
+  }
   return 0;
 }
 
@@ -320,7 +416,7 @@ int gadmm_chain_iterate(const GadmmChain* c, int n_iter, void* stream) {
   return 0;
 }
 
-int gadmm_chain_launches_per_iter(void) { return 3; }
+int gadmm_chain_launches_per_iter(void) { return 3; }   /* 5 with split_finish */
 
 int gadmm_chain_configure(void) {
   if (int e = configure_half<double>()) return e;

@@ -89,6 +89,11 @@ class ChainEngine:
         self.colpart = torch.empty((Nloc, cpe), dtype=f64, device=dev)
         self.counters = torch.zeros((Nloc + 1,), dtype=i32, device=dev)
         self.objw = torch.zeros((Nloc,), dtype=f64, device=dev)
+        # parallel finisher (csrc/gadmm_iter.cu: gadmm_finish_kernel) for d >= 512
+        self.split_finish = (dp // 64 >= 8) and os.environ.get("GADMM_B200_NO_SPLIT") != "1"
+        self.wready = torch.zeros((Nloc,), dtype=i64, device=dev)
+        self.sblk = torch.zeros((Nloc, dp // 64, 2), dtype=f64, device=dev)
+        self.fin_counters = torch.zeros((Nloc,), dtype=i32, device=dev)
         self.ctrl = torch.zeros((4,), dtype=i64, device=dev)
         self.obj_hist = torch.zeros((self.max_iter + 2,), dtype=f64, device=dev)
         self.loss_hist = torch.zeros((self.max_iter + 2,), dtype=f64, device=dev)
@@ -248,6 +253,9 @@ class ChainEngine:
         c.d, c.dp, c.Nglob, c.Nloc = self.d, self.dp, self.N, self.Nloc
         c.rank, c.nranks, c.store, c.max_iter = self.dist.rank, self.dist.world, self.store, self.max_iter
         c.pdl = int(self.pdl)
+        c.split_finish = int(self.split_finish)
+        c.wready, c.sblk, c.fin_counters = (self.wready.data_ptr(), self.sblk.data_ptr(),
+                                            self.fin_counters.data_ptr())
         self._desc = c
         return c
 
@@ -267,7 +275,7 @@ class ChainEngine:
                     nv.check(L.gadmm_chain_iterate(C.byref(c), int(n_iter), nv.stream_ptr()))
                 self._graphs[n_iter] = g    # capture does not execute; replay below does
             g.replay()
-        self.launches += 3 * int(n_iter)
+        self.launches += (5 if self.split_finish else 3) * int(n_iter)
 
     def run(self, num_iter: Optional[int] = None, window: int = 32, rechain=None,
             coherence: Optional[float] = None, use_graph: bool = True) -> int:
@@ -342,7 +350,7 @@ class ChainEngine:
                 g.replay()
             else:
                 launch(n)
-            self.launches += 5 * n
+            self.launches += (7 if self.split_finish else 5) * n
 
         done, base = 0, 1
         while done < num_iter:

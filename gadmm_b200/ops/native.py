@@ -35,7 +35,7 @@ class GadmmChain(C.Structure):
         ("rho", C.c_double), ("obj0", C.c_double), ("acc", C.c_double),
         ("d", C.c_int), ("dp", C.c_int), ("Nglob", C.c_int), ("Nloc", C.c_int), ("rank", C.c_int),
         ("nranks", C.c_int), ("store", C.c_int), ("max_iter", C.c_int), ("pdl", C.c_int),
-        ("reserved", C.c_int),
+        ("split_finish", C.c_int), ("wready", _vp), ("sblk", _vp), ("fin_counters", _vp),
     ]
 
 

@@ -112,7 +112,12 @@ typedef struct GadmmChain {
   int d, dp, Nglob, Nloc, rank, nranks, store, max_iter;
   int pdl;                   /* 1: tail and dual kernels use programmatic dependent launch; phase
                                 ordering on one GPU then also goes through the version flags */
-  int reserved;
+  int split_finish;          /* 1: the column-partial reduction / theta publication of every
+                                worker runs in gadmm_finish_kernel (one 64-thread CTA per 64
+                                entries) instead of in the worker's last streaming CTA */
+  unsigned long long* wready; /* [Nloc] iteration whose partial sums are complete (split_finish) */
+  double* sblk;              /* [Nloc][dp/64][2] per-block objective pieces (split_finish) */
+  unsigned int* fin_counters; /* [Nloc] zero-initialised (split_finish) */
 } GadmmChain;
 
 int gadmm_chain_half_iter(const GadmmChain* c, int color, void* stream);

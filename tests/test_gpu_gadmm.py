@@ -38,7 +38,7 @@ def test_gadmm_reference_shape(ref_linear, rho):
 
 def test_gadmm_odd_and_tiny_chains():
     rng = np.random.default_rng(5)
-    for N, s, d in ((1, 9, 5), (2, 9, 5), (3, 9, 5), (7, 20, 66)):
+    for N, s, d in ((1, 9, 5), (2, 9, 5), (3, 9, 5), (7, 20, 66), (4, 30, 530)):
         XX = rng.standard_normal((N * s, d))
         YY = rng.standard_normal(N * s)
         obj0 = O.opt_sol_closedForm(XX, YY)
