@@ -72,13 +72,16 @@ struct ChainX {
   }
 };
 
-template <typename T>
-__global__ void __launch_bounds__(kSymvThreads, 2)
+// NSTAGES = SymvCfg<T>::STAGES: two CTAs per SM (many workers per GPU).  NSTAGES doubled ("deep"):
+// one CTA per SM with twice the bytes in flight, for phases with fewer active CTAs than SMs
+// (one worker per GPU), where a 3-stage ring is latency-bound.
+template <typename T, int NSTAGES>
+__global__ void __launch_bounds__(kSymvThreads, (NSTAGES > SymvCfg<T>::STAGES) ? 1 : 2)
 gadmm_half_iter_kernel(const GadmmChain c, const int color) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
-  SymvSmem<T>& sm = *reinterpret_cast<SymvSmem<T>*>(smem_raw);
-  const int nT = c.dp / kT, npairs = (nT + 1) / 2;
-  const int k = blockIdx.x / npairs, p = blockIdx.x % npairs;
+  SymvSmem<T, NSTAGES>& sm = *reinterpret_cast<SymvSmem<T, NSTAGES>*>(smem_raw);
+  const int nT = c.dp / kT, npairs = (nT + 1) / 2, nsp = c.nsplit;
+  const int k = blockIdx.x / (npairs * nsp), p = (blockIdx.x / nsp) % npairs, part = blockIdx.x % nsp;
   if (c.color[k] != color) return;
   const unsigned long long it = c.ctrl[0];
   if (c.ctrl[2] != 0ull && c.ctrl[1] != 0ull) return;   // converged: freeze the state
@@ -105,10 +108,11 @@ gadmm_half_iter_kernel(const GadmmChain c, const int color) {
   xf.tr = r >= 0 ? c.theta + (slot_in + r) * c.dp : nullptr;
   xf.rho = c.rho;
 
-  double* rowpart = c.rowpart + (size_t)k * c.dp;
+  double* rowpart = c.rowpart + (size_t)k * nsp * c.dp;
   double* colpart = c.colpart + (size_t)k * colpart_elems(c.dp);
-  const bool last = symv_cta<T>(sm, reinterpret_cast<const T*>(c.Mptr[k]), nT, p, xf, rowpart,
-                                colpart, c.counters + k, npairs);
+  const bool last = symv_cta<T, ChainX, NSTAGES>(sm, reinterpret_cast<const T*>(c.Mptr[k]), nT, p,
+                                                 xf, rowpart + (size_t)part * c.dp, colpart,
+                                                 c.counters + k, npairs * nsp, part, nsp);
   if (!last) return;
   if (c.split_finish) {
     // the partial sums of worker k are complete: hand over to gadmm_finish_kernel (many CTAs)
@@ -128,7 +132,7 @@ gadmm_half_iter_kernel(const GadmmChain c, const int color) {
   const double crho = c.rho * (double)c.cmul[k];
   double s1 = 0.0, s2 = 0.0;
   for (int j = threadIdx.x; j < c.dp; j += blockDim.x) {
-    const double th = symv_gather(rowpart, colpart, nT, j);
+    const double th = symv_gather(rowpart, colpart, nT, j, nsp, c.dp);
     const double rj = xf(j);
     th_loc[j] = th;
     if (th_p0) th_p0[j] = th;          // NVLink P2P store into the neighbour GPU's replica
@@ -177,12 +181,12 @@ gadmm_finish_kernel(const GadmmChain c, const int color) {
   xf.tl = l >= 0 ? c.theta + (slot_in + l) * c.dp : nullptr;
   xf.tr = r >= 0 ? c.theta + (slot_in + r) * c.dp : nullptr;
   xf.rho = c.rho;
-  const double* rowpart = c.rowpart + (size_t)k * c.dp;
+  const double* rowpart = c.rowpart + (size_t)k * c.nsplit * c.dp;
   const double* colpart = c.colpart + (size_t)k * colpart_elems(c.dp);
   const size_t slot_out = (size_t)(it & 1ull) * c.Nglob;
   const int p0 = c.push0[k], p1 = c.push1[k];
   const int j = J * kT + tid;
-  const double th = symv_gather(rowpart, colpart, nT, j);
+  const double th = symv_gather(rowpart, colpart, nT, j, c.nsplit, c.dp);
   const double rj = xf(j);
   c.theta[(slot_out + g) * c.dp + j] = th;
   if (p0 >= 0) c.theta_peer[p0][(slot_out + g) * c.dp + j] = th;   // NVLink P2P stores
@@ -287,27 +291,22 @@ gadmm_dual_objective_kernel(const GadmmChain c) {
   }
 }
 
-template <typename T>
+template <typename T, int NSTAGES>
 static int configure_half() {
-  GADMM_CUDA_OK(cudaFuncSetAttribute(gadmm_half_iter_kernel<T>,
+  GADMM_CUDA_OK(cudaFuncSetAttribute(gadmm_half_iter_kernel<T, NSTAGES>,
                                      cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     (int)sizeof(SymvSmem<T>)));
+                                     (int)sizeof(SymvSmem<T, NSTAGES>)));
   return 0;
 }
 
-template <typename T>
-static int launch_half(const GadmmChain* c, int color, cudaStream_t st) {
-  static bool configured = false;
-  const int smem = (int)sizeof(SymvSmem<T>);
-  if (!configured) {
-    if (int e = configure_half<T>()) return e;
-    configured = true;
-  }
+template <typename T, int NSTAGES>
+static int launch_half_impl(const GadmmChain* c, int color, cudaStream_t st) {
+  const int smem = (int)sizeof(SymvSmem<T, NSTAGES>);
   const int nT = c->dp / kT, npairs = (nT + 1) / 2;
   if (c->pdl && color == 1) {
     // tail phase: programmatic dependent launch behind the head phase (ordering by flags)
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(c->Nloc * npairs);
+    cfg.gridDim = dim3(c->Nloc * npairs * c->nsplit);
     cfg.blockDim = dim3(kSymvThreads);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = st;
@@ -316,10 +315,27 @@ static int launch_half(const GadmmChain* c, int color, cudaStream_t st) {
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at;
     cfg.numAttrs = 1;
-    GADMM_CUDA_OK(cudaLaunchKernelEx(&cfg, gadmm_half_iter_kernel<T>, *c, color));
+    GADMM_CUDA_OK(cudaLaunchKernelEx(&cfg, gadmm_half_iter_kernel<T, NSTAGES>, *c, color));
   } else {
-    gadmm_half_iter_kernel<T><<<c->Nloc * npairs, kSymvThreads, smem, st>>>(*c, color);
+    gadmm_half_iter_kernel<T, NSTAGES><<<c->Nloc * npairs * c->nsplit, kSymvThreads, smem, st>>>(*c, color);
   }
+  return 0;
+}
+
+template <typename T>
+static int launch_half(const GadmmChain* c, int color, cudaStream_t st) {
+  static bool configured = false;
+  constexpr int S1 = SymvCfg<T>::STAGES, S2 = 2 * SymvCfg<T>::STAGES;
+  if (!configured) {
+    if (int e = configure_half<T, S1>()) return e;
+    if (int e = configure_half<T, S2>()) return e;
+    configured = true;
+  }
+  const int nT = c->dp / kT, npairs = (nT + 1) / 2;
+  // about half of the local workers are active per phase
+  const bool deep = c->nsplit == 1 && ((long long)c->Nloc * npairs + 1) / 2 <= 160;
+  if (int e = deep ? launch_half_impl<T, S2>(c, color, st) : launch_half_impl<T, S1>(c, color, st))
+    return e;
   GADMM_CUDA_OK(cudaGetLastError());
   if (c->split_finish) {
     cudaLaunchConfig_t cfg = {};
@@ -380,6 +396,7 @@ int gadmm_symv_batched(const void* const* Sptr, const double* x, double* y, int 
 int gadmm_chain_half_iter(const GadmmChain* c, int color, void* stream) {
   GADMM_REQUIRE(c && c->dp > 0 && c->dp % kT == 0, "chain: dp must be a positive multiple of 64");
   GADMM_REQUIRE(color == 0 || color == 1, "chain: color must be 0 or 1");
+  GADMM_REQUIRE(c->nsplit >= 1 && c->nsplit <= 8, "chain: nsplit must be in [1, 8]");
   if (c->Nloc <= 0) return 0;
   return c->store == GADMM_STORE_F64 ? launch_half<double>(c, color, (cudaStream_t)stream)
                                      : launch_half<float>(c, color, (cudaStream_t)stream);
@@ -419,8 +436,10 @@ int gadmm_chain_iterate(const GadmmChain* c, int n_iter, void* stream) {
 int gadmm_chain_launches_per_iter(void) { return 3; }   /* 5 with split_finish */
 
 int gadmm_chain_configure(void) {
-  if (int e = configure_half<double>()) return e;
-  return configure_half<float>();
+  if (int e = configure_half<double, SymvCfg<double>::STAGES>()) return e;
+  if (int e = configure_half<double, 2 * SymvCfg<double>::STAGES>()) return e;
+  if (int e = configure_half<float, SymvCfg<float>::STAGES>()) return e;
+  return configure_half<float, 2 * SymvCfg<float>::STAGES>();
 }
 
 }  // extern "C"

@@ -21,14 +21,18 @@ constexpr int kT = GADMM_TILE;           // 64
 constexpr int kConsumerWarps = 8;
 constexpr int kSymvThreads = (kConsumerWarps + 1) * 32;  // 288
 constexpr int kRowsPerWarp = kT / kConsumerWarps;        // 8
+#ifndef GADMM_BULK_SPLIT
+#define GADMM_BULK_SPLIT 1      // splitting a tile over several issuing lanes made no difference
+#endif
+constexpr int kBulkSplit = GADMM_BULK_SPLIT;
 
 template <typename T> struct SymvCfg;
 template <> struct SymvCfg<double> { static constexpr int STAGES = 3; };
 template <> struct SymvCfg<float>  { static constexpr int STAGES = 6; };
 
-template <typename T>
+template <typename T, int NSTAGES = SymvCfg<T>::STAGES>
 struct SymvSmem {
-  static constexpr int STAGES = SymvCfg<T>::STAGES;
+  static constexpr int STAGES = NSTAGES;
   alignas(128) T tile[STAGES][kT * kT];
   alignas(16) double xs[STAGES][kT];          // x_J slice travelling with each tile
   alignas(16) double xrow[2][kT];             // x_I slices of the CTA's two tile-rows
@@ -59,11 +63,14 @@ __device__ __forceinline__ double2 ld_pair(const float* p) {
 // CTA that completed matrix `k` last.  `xf(j)` yields element j of the input vector.
 //   S        packed matrix of this worker
 //   pairIdx  which pair of tile-rows (pairIdx, nT-1-pairIdx) this CTA owns
-template <typename T, typename XF>
-__device__ bool symv_cta(SymvSmem<T>& sm, const T* __restrict__ S, int nT, int pairIdx,
+template <typename T, typename XF, int NSTAGES = SymvCfg<T>::STAGES>
+__device__ bool symv_cta(SymvSmem<T, NSTAGES>& sm, const T* __restrict__ S, int nT, int pairIdx,
                          const XF& xf, double* __restrict__ rowpart, double* __restrict__ colpart,
-                         unsigned int* counter, int ctas_per_matrix) {
-  constexpr int STAGES = SymvSmem<T>::STAGES;
+                         unsigned int* counter, int ctas_per_matrix, int part = 0, int nparts = 1) {
+  // part / nparts: the tiles J of every tile-row are divided into `nparts` contiguous ranges, one
+  // CTA each (more CTAs in flight when a GPU holds few workers).  The row sums are then partial
+  // as well: `rowpart` must point at this part's own dp-vector and the gather adds the parts.
+  constexpr int STAGES = NSTAGES;
   constexpr uint32_t kTileBytes = kT * kT * sizeof(T);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 
@@ -85,39 +92,71 @@ __device__ bool symv_cta(SymvSmem<T>& sm, const T* __restrict__ S, int nT, int p
     // tiles of group g are issued), so the global-load latency of the fused RHS assembly never
     // sits between two bulk copies -- that matters when a GPU has few CTAs in flight (one worker
     // per GPU: 128 CTAs, each needing ~50 GB/s).
+// Register prefetch of the x slices one group ahead: measured 9 % SLOWER on the flagship shape
+// (1.464 vs 1.331 ms/iteration at 128 workers x d=4096 per GPU; same box A/B), so it is off.
+#ifndef GADMM_XPREFETCH
+#define GADMM_XPREFETCH 0
+#endif
     constexpr int kXG = 4;
     int stage = 0;
     uint32_t phase = 0;
+#if !GADMM_XPREFETCH
     for (int rr = 0; rr < nrows; ++rr) {
       const int I = rr == 0 ? rowA : rowB;
+      const int Jb = (int)(((long long)(I + 1) * part) / nparts);
+      const int Je = (int)(((long long)(I + 1) * (part + 1)) / nparts);
+      sm.xrow[rr][lane] = xf(I * kT + lane);
+      sm.xrow[rr][lane + 32] = xf(I * kT + lane + 32);
+      const T* rowbase = S + ((size_t)I * (I + 1) / 2) * (kT * kT);
+      for (int J = Jb; J < Je; ++J) {
+        mbar_wait(&sm.empty[stage], phase ^ 1);
+        if (lane == 0) bulk_g2s(sm.tile[stage], rowbase + (size_t)J * (kT * kT), kTileBytes, &sm.full[stage]);
+        sm.xs[stage][lane] = xf(J * kT + lane);
+        sm.xs[stage][lane + 32] = xf(J * kT + lane + 32);
+        __syncwarp();
+        if (lane == 0) mbar_arrive_expect_tx(&sm.full[stage], kTileBytes);
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      }
+    }
+#else
+    for (int rr = 0; rr < nrows; ++rr) {
+      const int I = rr == 0 ? rowA : rowB;
+      const int Jb = (int)(((long long)(I + 1) * part) / nparts);
+      const int Je = (int)(((long long)(I + 1) * (part + 1)) / nparts);     // tiles [Jb, Je)
       double cur[2 * kXG], nxt[2 * kXG];
 #pragma unroll
       for (int q = 0; q < kXG; ++q) {
-        const bool ok = q <= I;
-        nxt[2 * q] = ok ? xf(q * kT + lane) : 0.0;
-        nxt[2 * q + 1] = ok ? xf(q * kT + lane + 32) : 0.0;
+        const bool ok = Jb + q < Je;
+        nxt[2 * q] = ok ? xf((Jb + q) * kT + lane) : 0.0;
+        nxt[2 * q + 1] = ok ? xf((Jb + q) * kT + lane + 32) : 0.0;
       }
       // x_I slice for the column products of this tile-row
       sm.xrow[rr][lane] = xf(I * kT + lane);
       sm.xrow[rr][lane + 32] = xf(I * kT + lane + 32);
       const T* rowbase = S + ((size_t)I * (I + 1) / 2) * (kT * kT);
-      for (int J0 = 0; J0 <= I; J0 += kXG) {
+      for (int J0 = Jb; J0 < Je; J0 += kXG) {
 #pragma unroll
         for (int q = 0; q < 2 * kXG; ++q) cur[q] = nxt[q];
 #pragma unroll
         for (int q = 0; q < kXG; ++q) {            // prefetch the next group's slices
           const int Jn = J0 + kXG + q;
-          const bool ok = Jn <= I;
+          const bool ok = Jn < Je;
           nxt[2 * q] = ok ? xf(Jn * kT + lane) : 0.0;
           nxt[2 * q + 1] = ok ? xf(Jn * kT + lane + 32) : 0.0;
         }
 #pragma unroll
         for (int q = 0; q < kXG; ++q) {
           const int J = J0 + q;
-          if (J > I) break;
+          if (J >= Je) break;
           mbar_wait(&sm.empty[stage], phase ^ 1);
-          if (lane == 0) bulk_g2s(sm.tile[stage], rowbase + (size_t)J * (kT * kT), kTileBytes,
-                                  &sm.full[stage]);
+          // one tile = kBulkSplit bulk copies issued by different lanes: copies issued by one
+          // thread were observed to execute back to back (~25 GB/s per CTA), which starves
+          // phases with few CTAs per GPU; independent issuers overlap
+          if (lane < kBulkSplit)
+            bulk_g2s(reinterpret_cast<unsigned char*>(sm.tile[stage]) + lane * (kTileBytes / kBulkSplit),
+                     reinterpret_cast<const unsigned char*>(rowbase + (size_t)J * (kT * kT)) +
+                         lane * (kTileBytes / kBulkSplit),
+                     kTileBytes / kBulkSplit, &sm.full[stage]);
           sm.xs[stage][lane] = cur[2 * q];
           sm.xs[stage][lane + 32] = cur[2 * q + 1];
           __syncwarp();
@@ -126,6 +165,7 @@ __device__ bool symv_cta(SymvSmem<T>& sm, const T* __restrict__ S, int nT, int p
         }
       }
     }
+#endif
   } else {
     // ------------------------------------------------------------------ consumer warps
     int stage = 0;
@@ -137,9 +177,11 @@ __device__ bool symv_cta(SymvSmem<T>& sm, const T* __restrict__ S, int nT, int p
       double xr[kRowsPerWarp];
 #pragma unroll
       for (int r = 0; r < kRowsPerWarp; ++r) acc_row[r] = 0.0;
-      for (int J = 0; J <= I; ++J, ++t) {
+      const int Jb = (int)(((long long)(I + 1) * part) / nparts);
+      const int Je = (int)(((long long)(I + 1) * (part + 1)) / nparts);
+      for (int J = Jb; J < Je; ++J, ++t) {
         mbar_wait(&sm.full[stage], phase);
-        if (J == 0) {
+        if (J == Jb) {
 #pragma unroll
           for (int r = 0; r < kRowsPerWarp; ++r) xr[r] = sm.xrow[rr][warp * kRowsPerWarp + r];
         }
@@ -194,9 +236,10 @@ __device__ bool symv_cta(SymvSmem<T>& sm, const T* __restrict__ S, int nT, int p
 
 // y_j = rowpart[j] + sum_{I > j/64} colpart(I, j/64)[j%64], fixed order (deterministic).
 __device__ __forceinline__ double symv_gather(const double* rowpart, const double* colpart, int nT,
-                                              int j) {
+                                              int j, int nparts = 1, size_t part_stride = 0) {
   const int J = j / kT, jj = j % kT;
   double v = __ldcg(rowpart + j);
+  for (int q = 1; q < nparts; ++q) v += __ldcg(rowpart + q * part_stride + j);
 #pragma unroll 8
   for (int I = J + 1; I < nT; ++I) v += __ldcg(colpart + colpart_off(I, J) + jj);   // loads overlap
   return v;

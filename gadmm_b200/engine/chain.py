@@ -85,7 +85,14 @@ class ChainEngine:
         self.hyy = torch.zeros((Nloc,), dtype=f64, device=dev)
         self.nu = torch.zeros((Nloc, dp), dtype=f64, device=dev)
         cpe = max(1, (dp // 64) * (dp // 64 - 1) // 2 * 64)
-        self.rowpart = torch.empty((Nloc, dp), dtype=f64, device=dev)
+        # few workers per GPU: divide every tile-row pair over several CTAs so that ~2 CTAs per SM
+        # are streaming (a single CTA sustains ~25 GB/s)
+        active = max(1, (Nloc * ((dp // 64 + 1) // 2) + 1) // 2)
+        want = max(1, -(-296 // active))
+        self.nsplit = int(min(8, 1 << (want - 1).bit_length())) if dp // 64 >= 8 else 1
+        if os.environ.get("GADMM_B200_NSPLIT"):
+            self.nsplit = int(os.environ["GADMM_B200_NSPLIT"])
+        self.rowpart = torch.empty((Nloc, self.nsplit, dp), dtype=f64, device=dev)
         self.colpart = torch.empty((Nloc, cpe), dtype=f64, device=dev)
         self.counters = torch.zeros((Nloc + 1,), dtype=i32, device=dev)
         self.objw = torch.zeros((Nloc,), dtype=f64, device=dev)
@@ -254,6 +261,7 @@ class ChainEngine:
         c.rank, c.nranks, c.store, c.max_iter = self.dist.rank, self.dist.world, self.store, self.max_iter
         c.pdl = int(self.pdl)
         c.split_finish = int(self.split_finish)
+        c.nsplit = int(self.nsplit)
         c.wready, c.sblk, c.fin_counters = (self.wready.data_ptr(), self.sblk.data_ptr(),
                                             self.fin_counters.data_ptr())
         self._desc = c

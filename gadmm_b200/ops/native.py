@@ -36,6 +36,7 @@ class GadmmChain(C.Structure):
         ("d", C.c_int), ("dp", C.c_int), ("Nglob", C.c_int), ("Nloc", C.c_int), ("rank", C.c_int),
         ("nranks", C.c_int), ("store", C.c_int), ("max_iter", C.c_int), ("pdl", C.c_int),
         ("split_finish", C.c_int), ("wready", _vp), ("sblk", _vp), ("fin_counters", _vp),
+        ("nsplit", C.c_int), ("reserved", C.c_int),
     ]
 
 
@@ -44,7 +45,9 @@ def lib():
     if _lib is not None:
         return _lib
     path = lib_path()
-    if needs_build():
+    if os.environ.get("GADMM_B200_LIB"):          # A/B experiments with an alternative build
+        path = os.environ["GADMM_B200_LIB"]
+    elif needs_build():
         if os.environ.get("GADMM_B200_NO_BUILD") == "1" and os.path.exists(path):
             pass
         else:

@@ -97,7 +97,7 @@ typedef struct GadmmChain {
   unsigned long long* objflag; /* [4][nranks] */
   double* const* objpart_peer;            /* [nranks] */
   unsigned long long* const* objflag_peer; /* [nranks] */
-  double* rowpart;           /* scratch [Nloc][dp] */
+  double* rowpart;           /* scratch [Nloc][nsplit][dp] */
   double* colpart;           /* scratch [Nloc][dp*dp/128] */
   unsigned int* counters;    /* [Nloc+1] zero-initialised */
   double* objw;              /* [Nloc] per-worker objective of the current iteration */
@@ -118,6 +118,9 @@ typedef struct GadmmChain {
   unsigned long long* wready; /* [Nloc] iteration whose partial sums are complete (split_finish) */
   double* sblk;              /* [Nloc][dp/64][2] per-block objective pieces (split_finish) */
   unsigned int* fin_counters; /* [Nloc] zero-initialised (split_finish) */
+  int nsplit;                /* >= 1: CTAs per pair of tile-rows (tile columns divided into nsplit
+                                ranges); rowpart is then [Nloc][nsplit][dp] */
+  int reserved;
 } GadmmChain;
 
 int gadmm_chain_half_iter(const GadmmChain* c, int color, void* stream);
