@@ -114,8 +114,43 @@ def logistic(D, a):
          Iter=int(r[2]), wall_s=time.perf_counter() - t0, final_loss=float(r[1][-1]))
 
 
+def baselines_scaled(D, a):
+    """Config 2, the "vs" list at the scaled shape on ONE GPU: iteration rate of every first-order
+    baseline (gradient provider = streaming SYMV over all packed Grams + one fused update kernel)."""
+    if D.rank != 0:
+        return
+    import torch
+    from gadmm_b200.engine.scaled import build_scaled_first_order
+    from gadmm_b200.ops import native as nv
+    N, d, s, T = a.bl_workers, a.bl_d, a.bl_s, a.bl_iters
+    t0 = time.time()
+    fo, obj0 = build_scaled_first_order(N, d, s)
+    alpha = 1.0 / fo.lambda_max(tol=1e-9, max_it=400)
+    Hmax = fo.hmax_per_worker(30)
+    setup = time.time() - t0
+    thr = 10.0 / (alpha ** 2 * N ** 2) / 10
+    runs = (("GD", lambda: fo.run_shared(nv.FO_GD, alpha, 0.0, Hmax, T, obj0, None)),
+            ("LAG-PS", lambda: fo.run_shared(nv.FO_LAG_PS, alpha, thr, Hmax, T, obj0, None)),
+            ("LAG-WK", lambda: fo.run_shared(nv.FO_LAG_WK, alpha, thr / 10, Hmax, T, obj0, None)),
+            ("cyclic IAG", lambda: fo.run_shared(nv.FO_IAG_CYCLIC, alpha / N, 0.0, Hmax, T, obj0, None)),
+            ("DGD", lambda: fo.run_dgd(alpha / 100, T, obj0)),
+            ("dual averaging", lambda: fo.run_dualavg(alpha, T, obj0, 1e-4)))
+    for name, fn in runs:
+        r = fn()
+        tv = r[3] if name == "dual averaging" else r[2]
+        loss = r[1]
+        emit(D, config=f"baselines N={N} d={d} s={s} (1 GPU)", algo=name, iters=len(loss),
+             ms_per_iter=1e3 * float(tv[-1]) / max(len(tv) - 1, 1), loss_first=float(loss[0]),
+             loss_last=float(loss[-1]), setup_s=setup,
+             uploads=(float(r[3][-1]) if name.startswith("LAG") else None))
+
+
 def main():
     ap = argparse.ArgumentParser()
+    ap.add_argument("--bl-workers", type=int, default=1024)
+    ap.add_argument("--bl-d", type=int, default=4096)
+    ap.add_argument("--bl-s", type=int, default=1024)
+    ap.add_argument("--bl-iters", type=int, default=60)
     ap.add_argument("--which", default="all")
     ap.add_argument("--dg-workers", type=int, default=64)
     ap.add_argument("--dg-iters", type=int, default=6000)
@@ -133,7 +168,8 @@ def main():
     D = Dist()
     todo = a.which.split(",")
     for name, fn in (("reference", reference_shape), ("dgadmm", dgadmm),
-                     ("t3", one_worker_per_gpu), ("logistic", logistic)):
+                     ("t3", one_worker_per_gpu), ("logistic", logistic),
+                     ("baselines", baselines_scaled)):
         if "all" in todo or name in todo:
             fn(D, a)
             D.barrier()

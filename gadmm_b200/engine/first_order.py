@@ -42,6 +42,41 @@ class FirstOrder:
         self.fw = torch.zeros((N,), dtype=torch.float64, device=self.dev)
         self.launches = 0
 
+    @classmethod
+    def from_parts(cls, P, b, hyy, Gsum, N, d, device=None):
+        """Least-squares engine from device-resident pieces (packed Grams ``P`` (N, packed), ``b``
+        (N, dp), ``0.5 y'y`` (N,), ``sum_n G_n`` (dp, dp)): the scaled configs never hold X."""
+        self = cls.__new__(cls)
+        self.dev = device or P.device
+        self.N, self.d, self.s, self.logistic, self.lam = int(N), int(d), 0, False, 0.0
+        self.dp = nv.padded(self.d)
+        self.P, self.b, self.hyy, self.Gsum = P, b, hyy, Gsum
+        self.store = nv.STORE_F64 if P.dtype == torch.float64 else nv.STORE_F32
+        self.ptrs = LA.ptr_table(P)
+        self.scratch = torch.empty((N, nv.symv_scratch_elems(self.dp)), dtype=torch.float64,
+                                   device=self.dev)
+        self.cnt = torch.zeros((N,), dtype=torch.int32, device=self.dev)
+        self.Y = torch.zeros((N, self.dp), dtype=torch.float64, device=self.dev)
+        self.fw = torch.zeros((N,), dtype=torch.float64, device=self.dev)
+        self.launches = 0
+        return self
+
+    def hmax_per_worker(self, iters: int = 60) -> np.ndarray:
+        """``Hmax(i) = max(eig(X{i}'*X{i}))`` for every worker at once: batched power iteration on
+        the packed Grams (LinearRegression_Synthetic.m:33)."""
+        mv = LA.BatchedSymv(self.P, self.dp)
+        g = torch.Generator(device=self.dev)
+        g.manual_seed(1)
+        v = torch.zeros((self.N, self.dp), dtype=torch.float64, device=self.dev)
+        v[:, :self.d] = torch.rand((self.N, self.d), dtype=torch.float64, device=self.dev, generator=g) + 0.5
+        v /= v.norm(dim=1, keepdim=True)
+        w = torch.empty_like(v)
+        for _ in range(iters):
+            mv(v, out=w)
+            lam = (v * w).sum(1)
+            v = w / w.norm(dim=1, keepdim=True)
+        return lam.cpu().numpy()
+
     # ---------------------------------------------------------------------------------------
     def lambda_max(self, tol: float = 1e-15, max_it: int = 50000) -> float:
         """Largest eigenvalue of ``X'X = sum_n G_n`` by power iteration on the packed Gram with the

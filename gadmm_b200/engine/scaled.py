@@ -109,3 +109,42 @@ def _build_scaled_tc(eng: ChainEngine, s: int, seed: int, noise: float, verbose:
     eng.obj0 = obj0
     eng._desc = None
     return obj0
+
+
+def build_scaled_first_order(N: int, d: int, s: int, seed: int = 0, noise: float = 0.1, dev=None,
+                             store: str = "f64", batch: int = 16):
+    """The data set of :func:`build_scaled_linreg` (same per-batch generator seeds) reduced to packed
+    Gram matrices for the first-order baselines (GD / DGD / LAG / IAG / dual averaging at the scaled
+    shape, BASELINE.json config 2).  Single GPU: the packed Grams of 1024 x 4096 take 69.8 GB.
+    Returns ``(FirstOrder engine, obj0)``."""
+    from .first_order import FirstOrder
+    dev = dev or torch.device("cuda", torch.cuda.current_device())
+    dp = nv.padded(d)
+    gen = torch.Generator(device=dev)
+    gen.manual_seed(1234)
+    theta_true = torch.randn(d, dtype=torch.float64, device=dev, generator=gen)
+    st = nv.STORE_F64 if store == "f64" else nv.STORE_F32
+    P = torch.empty((N, nv.packed_elems(dp)), dtype=torch.float64 if store == "f64" else torch.float32,
+                    device=dev)
+    b = torch.zeros((N, dp), dtype=torch.float64, device=dev)
+    hyy = torch.zeros((N,), dtype=torch.float64, device=dev)
+    Gsum = torch.zeros((dp, dp), dtype=torch.float64, device=dev)
+    scale = 1.0 / np.sqrt(s)
+    for k0 in range(0, N, batch):
+        nb = min(batch, N - k0)
+        gen.manual_seed(seed * 1000003 + k0)
+        X = torch.randn((nb, s, d), dtype=torch.float32, device=dev, generator=gen).double()
+        X *= scale
+        y = torch.einsum("nsd,d->ns", X, theta_true)
+        y += noise * torch.randn((nb, s), dtype=torch.float64, device=dev, generator=gen)
+        G, bb, hh = LA.gram(X, y, dp)
+        del X
+        LA.pack_sym(G, d, st, out=P[k0:k0 + nb])
+        b[k0:k0 + nb], hyy[k0:k0 + nb] = bb, hh
+        Gsum += G.sum(0)
+        del G
+    A = LA.shifted_inverse(Gsum.unsqueeze(0), d, 0.0)
+    th = LA.BatchedSymv(LA.pack_sym(A, d), dp)(b.sum(0).unsqueeze(0))[0]
+    bs = b.sum(0)
+    obj0 = 0.5 * float(th @ (Gsum @ th)) - float(bs @ th) + float(hyy.sum())
+    return FirstOrder.from_parts(P, b, hyy, Gsum, N, d, dev), obj0
