@@ -124,11 +124,12 @@ shared_update_kernel(const GadmmShared p) {
   if (p.ctrl[2] != 0ull && p.ctrl[1] != 0ull) return;
   if (it > (unsigned long long)p.max_iter) return;
   const int n = blockIdx.x, tid = threadIdx.x, dp = p.dp;
+  const int gn = p.gid0 + n;                  // global worker id (workers are split over the GPUs)
   const double* fresh = p.Y + (size_t)n * dp;
   double* gh = p.ghat + (size_t)n * dp;
 
   if (p.kind == GADMM_FO_LAG_PS || p.kind == GADMM_FO_LAG_WK) {
-    if (p.kind == GADMM_FO_LAG_PS && n == 0 && it > 1ull)        // GD_DGD_LAG.m:204-209
+    if (p.kind == GADMM_FO_LAG_PS && gn == 0 && it > 1ull)       // GD_DGD_LAG.m:204-209
       for (int j = tid; j < dp; j += 256) gh[j] = fresh[j];
     if (it > (unsigned long long)kSlots) {
       double trig = 0.0;
@@ -149,22 +150,20 @@ shared_update_kernel(const GadmmShared p) {
           gh[j] = fresh[j];
           if (p.kind == GADMM_FO_LAG_PS) p.theta_hat[(size_t)n * dp + j] = p.theta[j];
         }
-        if (tid == 0) {
-          atomicAdd(p.ctrl + 3, 1ull);
-          atomicExch(p.counters + 1, 1u);
-        }
+        if (tid == 0) atomicAdd(p.counters + 1, 1u);          // uploads of this iteration
       }
     }
   } else if (p.kind == GADMM_FO_IAG_CYCLIC) {
-    if (it > 1ull && n == (int)(it % (unsigned long long)p.N))   // i=mod(iter,N)+1 (:337)
+    if (it > 1ull && gn == (int)(it % (unsigned long long)p.Nglob))   // i=mod(iter,N)+1 (:337)
       for (int j = tid; j < dp; j += 256) gh[j] = fresh[j];
   } else if (p.kind == GADMM_FO_IAG_RANDOM) {
     const double u = p.uni[it];
     int i = 0;
-    while (i < p.N - 1 && !(u <= p.cumprob[i])) ++i;             // :356-360
-    if (it > 1ull && n == i)
+    while (i < p.Nglob - 1 && !(u <= p.cumprob[i])) ++i;         // :356-360
+    if (it > 1ull && gn == i)
       for (int j = tid; j < dp; j += 256) gh[j] = fresh[j];
   }
+  if (p.split_server) return;                  // server stage runs in shared_server_kernel
   // ------------------------------------------------------------------ server (last CTA)
   __threadfence();
   __syncthreads();
@@ -196,11 +195,123 @@ shared_update_kernel(const GadmmShared p) {
     p.loss_hist[it] = loss;
     p.t_hist[it] = globaltimer_ns();
     if (p.kind == GADMM_FO_LAG_PS || p.kind == GADMM_FO_LAG_WK) {
+      p.ctrl[3] += (unsigned long long)p.counters[1];
       if (p.counters[1] == 0u && it % 1000ull == 0ull) p.ctrl[3] += 1ull;   // idle bump (:246-251)
       p.comm_hist[it] = (double)p.ctrl[3];
     }
     p.counters[0] = 0u;
     p.counters[1] = 0u;
+    if (loss < p.acc && p.ctrl[1] == 0ull) p.ctrl[1] = it;
+    p.ctrl[0] = it + 1ull;
+  }
+}
+
+// ------------------------------------------------- shared-iterate server, parallel + multi-GPU
+// grid = dp/64 CTAs x 256 threads (4 worker groups x 64 columns).  Phase 1: column sums of the
+// local workers' (stale) gradients; with several GPUs every CTA pushes its 64 partial sums into
+// all peers' `xbuf` (NVLink P2P stores), the last CTA adds this GPU's objective partial and upload
+// count and raises the per-rank flag on every GPU.  Phase 2: all CTAs wait for all ranks' flags,
+// add the partials in rank order (identical result everywhere -> the server step is replicated,
+// no broadcast), step theta, and the last CTA closes the iteration.  This is the fused
+// reduce + update of SURVEY.md K7.
+__global__ void __launch_bounds__(256)
+shared_server_kernel(const GadmmShared p) {
+  __shared__ double part[4][64];
+  __shared__ double red[32];
+  __shared__ unsigned int ticket;
+  const unsigned long long it = p.ctrl[0];
+  if (p.ctrl[2] != 0ull && p.ctrl[1] != 0ull) return;
+  if (it > (unsigned long long)p.max_iter) return;
+  const int tid = threadIdx.x, col = tid & 63, grp = tid >> 6, dp = p.dp;
+  const int j = blockIdx.x * 64 + col;
+  const size_t row = (size_t)dp + 64;
+  const size_t slot = (size_t)(it & 1ull) * p.nranks * row;
+  // ---- phase 1: local column sums (fixed partition of the workers into 4 contiguous groups)
+  double S = 0.0;
+  const int n0 = (p.N * grp) / 4, n1 = (p.N * (grp + 1)) / 4;
+  if (p.kind == GADMM_FO_GD) {
+    if (it > 1ull) { for (int n = n0; n < n1; ++n) S += __ldcg(p.Y + (size_t)n * dp + j); }
+    else if (grp == 0 && p.gid0 == 0) S = p.logistic ? __ldcg(p.Y + j) : (j < p.d ? 1.0 : 0.0);
+  } else {
+    for (int n = n0; n < n1; ++n) S += __ldcg(p.ghat + (size_t)n * dp + j);
+  }
+  part[grp][col] = S;
+  __syncthreads();
+  S = (part[0][col] + part[1][col]) + (part[2][col] + part[3][col]);
+  if (p.nranks > 1) {
+    if (grp == 0)
+      for (int q = 0; q < p.nranks; ++q) p.xbuf_peer[q][slot + (size_t)p.rank * row + j] = S;
+    __threadfence_system();
+    __syncthreads();
+    if (tid == 0) ticket = atomicAdd(p.counters2, 1u);
+    __syncthreads();
+    if (ticket == gridDim.x - 1) {              // this GPU's partials are all written
+      double f = 0.0;
+      for (int i = tid; i < p.N; i += 256) f += __ldcg(p.fw + i);
+      f = block_sum(f, red);
+      if (tid == 0) {
+        p.counters2[0] = 0u;
+        for (int q = 0; q < p.nranks; ++q) {
+          double* dst = p.xbuf_peer[q] + slot + (size_t)p.rank * row + dp;
+          dst[0] = f;
+          dst[1] = (double)p.counters[1];
+        }
+        __threadfence_system();
+        for (int q = 0; q < p.nranks; ++q)
+          st_release_sys(p.xflag_peer[q] + (it & 1ull) * p.nranks + p.rank, it);
+      }
+    }
+    // ---- phase 2: wait for every rank, add in rank order
+    if (tid == 0)
+      for (int q = 0; q < p.nranks; ++q) wait_flag_ge(p.xflag + (it & 1ull) * p.nranks + q, it);
+    __syncthreads();
+    S = 0.0;
+    for (int q = 0; q < p.nranks; ++q) S += __ldcg(p.xbuf + slot + (size_t)q * row + j);
+  }
+  double dn = 0.0;
+  if (grp == 0) {
+    const double step = p.step * S;
+    p.theta[j] -= step;
+    dn = step * step;
+  }
+  dn = block_sum(dn, red);
+  if (tid == 0) {
+    p.dnpart[blockIdx.x] = dn;
+    __threadfence();
+    ticket = atomicAdd(p.counters2 + 1, 1u);
+  }
+  __syncthreads();
+  if (ticket != gridDim.x - 1) return;
+  // ---- last CTA: close the iteration
+  double f = 0.0;
+  if (p.nranks == 1)
+    for (int i = tid; i < p.N; i += 256) f += __ldcg(p.fw + i);
+  f = block_sum(f, red);
+  if (tid == 0) {
+    double dtot = 0.0;
+    for (int b2 = 0; b2 < (int)gridDim.x; ++b2) dtot += __ldcg(p.dnpart + b2);
+    unsigned long long up = p.counters[1];
+    if (p.nranks > 1) {
+      f = 0.0;
+      up = 0ull;
+      for (int q = 0; q < p.nranks; ++q) {
+        f += __ldcg(p.xbuf + slot + (size_t)q * row + dp);
+        up += (unsigned long long)__ldcg(p.xbuf + slot + (size_t)q * row + dp + 1);
+      }
+    }
+    p.dnorm[it % kSlots] = dtot;
+    const double loss = fabs(f - p.obj0);
+    p.obj_hist[it] = f;
+    p.loss_hist[it] = loss;
+    p.t_hist[it] = globaltimer_ns();
+    if (p.kind == GADMM_FO_LAG_PS || p.kind == GADMM_FO_LAG_WK) {
+      p.ctrl[3] += up;
+      if (up == 0ull && it % 1000ull == 0ull) p.ctrl[3] += 1ull;            // idle bump
+      p.comm_hist[it] = (double)p.ctrl[3];
+    }
+    p.counters[0] = 0u;
+    p.counters[1] = 0u;
+    p.counters2[1] = 0u;
     if (loss < p.acc && p.ctrl[1] == 0ull) p.ctrl[1] = it;
     p.ctrl[0] = it + 1ull;
   }
@@ -357,7 +468,10 @@ int gadmm_logistic_grad(const double* X, const double* y, const double* th, long
 
 int gadmm_shared_update(const GadmmShared* p, void* stream) {
   GADMM_REQUIRE(p && p->N > 0, "shared_update: N must be positive");
+  GADMM_REQUIRE(p->split_server || p->nranks == 1, "shared_update: multi-GPU needs split_server");
   shared_update_kernel<<<p->N, 256, 0, (cudaStream_t)stream>>>(*p);
+  if (p->split_server)
+    shared_server_kernel<<<p->dp / 64, 256, 0, (cudaStream_t)stream>>>(*p);
   GADMM_CUDA_OK(cudaGetLastError());
   return 0;
 }

@@ -13,12 +13,14 @@ def _as_rng(rng):
     return rng if isinstance(rng, np.random.Generator) else np.random.default_rng(rng)
 
 
-def _six(fo: FirstOrder, alpha, Hmax, N, T, obj0, accuracy, rng):
+def _six(fo: FirstOrder, alpha, Hmax, N, T, obj0, accuracy, rng, fo_own=None):
     thrd = 10.0 / (alpha ** 2 * N ** 2) / TRIGGERSLOT          # GD_DGD_LAG.m:47
     thrd5 = 1.0 / (alpha ** 2 * N ** 2) / TRIGGERSLOT          # :65
     nonprob = Hmax / Hmax.sum()
     uni = np.concatenate([[0.0], _as_rng(rng).random(T), [0.0]])
-    o_dgd = fo.run_dgd(alpha / 100.0, T, obj0)                 # :127
+    if fo.dist is not None:
+        uni = fo.dist.broadcast_object(uni)      # every GPU must sample the same worker
+    o_dgd = (fo_own or fo).run_dgd(alpha / 100.0, T, obj0)     # :127 (chain stencil: one GPU)
     ps = fo.run_shared(nv.FO_LAG_PS, alpha, thrd, Hmax, T, obj0, accuracy)
     wk = fo.run_shared(nv.FO_LAG_WK, alpha, thrd5, Hmax, T, obj0, accuracy)
     cy = fo.run_shared(nv.FO_IAG_CYCLIC, alpha / N, 0.0, Hmax, T, obj0, accuracy)
@@ -27,30 +29,48 @@ def _six(fo: FirstOrder, alpha, Hmax, N, T, obj0, accuracy, rng):
     return o_dgd, ps, wk, cy, ra
 
 
+def _dist_or_none(dist):
+    if dist is not None:
+        return dist if dist.world > 1 else None
+    import os
+    if int(os.environ.get("WORLD_SIZE", "1")) > 1:
+        from ..parallel.runtime import Dist
+        return Dist()
+    return None
+
+
 def gd_dgd_lag(X, y, num_workers, num_feature, Hmax, num_iter, obj0, X_fede, y_fede, num_sample,
-               rng=None, store="f64"):
-    """GPU ``GD_DGD_LAG`` (19 outputs, GD_DGD_LAG.m:1-4)."""
+               rng=None, store="f64", dist=None):
+    """GPU ``GD_DGD_LAG`` (19 outputs, GD_DGD_LAG.m:1-4).  Under torchrun the parameter-server
+    methods (GD, LAG-PS, LAG-WK, IAG) split the workers over the GPUs and reduce inside the server
+    kernel through NVLink peer stores; DGD runs replicated on every GPU."""
     N, d, T = int(num_workers), int(num_feature), int(num_iter)
-    fo = FirstOrder(X_fede, y_fede, N, d, num_sample, logistic=False, store=store)
+    dist = _dist_or_none(dist)
+    fo = FirstOrder(X_fede, y_fede, N, d, num_sample, logistic=False, store=store, dist=dist)
+    fo_own = FirstOrder(X_fede, y_fede, N, d, num_sample, logistic=False, store=store) \
+        if dist is not None else None
     Hmax = np.asarray(Hmax, dtype=np.float64).reshape(-1)[:N]
     alpha = 1.0 / fo.lambda_max()                              # :19,46
     gd = fo.run_shared(nv.FO_GD, alpha, 0.0, Hmax, T, obj0, None)
-    dgd, ps, wk, cy, ra = _six(fo, alpha, Hmax, N, T, obj0, None, rng)
+    dgd, ps, wk, cy, ra = _six(fo, alpha, Hmax, N, T, obj0, None, rng, fo_own)
     return (gd[0], gd[1], gd[2], dgd[0], dgd[1], dgd[2], ps[0], ps[1], ps[2], ps[3],
             wk[0], wk[1], wk[2], wk[3], cy[0], cy[1], ra[0], ra[1], alpha)
 
 
 def gd_dgd_lag_logistic(X, y, num_workers, num_feature, Hmax, num_iter, X_fede, y_fede, num_sample,
-                        lam, accuracy, rng=None, naive=True):
+                        lam, accuracy, rng=None, naive=True, dist=None):
     """GPU ``GD_DGD_LAG_logistic`` (20 outputs; ``obj1`` = GD's last objective, :131-133)."""
     N, d, T = int(num_workers), int(num_feature), int(num_iter)
-    fo = FirstOrder(X_fede, y_fede, N, d, num_sample, logistic=True, lam=lam)
+    dist = _dist_or_none(dist)
+    fo = FirstOrder(X_fede, y_fede, N, d, num_sample, logistic=True, lam=lam, dist=dist)
+    fo_own = FirstOrder(X_fede, y_fede, N, d, num_sample, logistic=True, lam=lam) \
+        if dist is not None else None
     Hmax = np.asarray(Hmax, dtype=np.float64).reshape(-1)[:N]
     alpha = 1.0 / (0.25 * fo.lambda_max() + lam)               # :24
     gd = fo.run_shared(nv.FO_GD, alpha, 0.0, Hmax, T, 0.0, None)
     obj1 = float(gd[0][-1])
     loss_gd = np.abs(gd[0] - obj1)
-    dgd, ps, wk, cy, ra = _six(fo, alpha, Hmax, N, T, obj1, accuracy, rng)
+    dgd, ps, wk, cy, ra = _six(fo, alpha, Hmax, N, T, obj1, accuracy, rng, fo_own)
     return (gd[0], loss_gd, gd[2], dgd[0], dgd[1], dgd[2], ps[0], ps[1], ps[2], ps[3],
             wk[0], wk[1], wk[2], wk[3], cy[0], cy[1], ra[0], ra[1], alpha, obj1)
 

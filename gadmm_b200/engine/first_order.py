@@ -18,16 +18,33 @@ from ..ops import native as nv
 
 
 class FirstOrder:
-    def __init__(self, XX, YY, N, d, s, logistic=False, lam=0.0, device=None, store="f64"):
-        self.dev = device or torch.device("cuda", torch.cuda.current_device())
-        self.N, self.d, self.s, self.logistic, self.lam = int(N), int(d), int(s), logistic, float(lam)
-        self.dp = nv.padded(self.d)
+    def __init__(self, XX, YY, N, d, s, logistic=False, lam=0.0, device=None, store="f64",
+                 dist=None):
+        """``dist`` (a :class:`gadmm_b200.parallel.runtime.Dist` with world > 1) splits the workers
+        into contiguous id ranges over the GPUs for the shared-iterate methods; ``dist=None`` keeps
+        every worker on this GPU."""
+        self.dist = dist if (dist is not None and dist.world > 1) else None
+        self.dev = device or (dist.device if dist is not None else
+                              torch.device("cuda", torch.cuda.current_device()))
+        self.Nglob, self.gid0 = int(N), 0
         XX = np.asarray(XX, dtype=np.float64)[: N * s, :d]
         YY = np.asarray(YY, dtype=np.float64).reshape(-1)[: N * s]
+        if self.dist is not None:
+            from ..parallel.runtime import partition
+            own = np.nonzero(partition(int(N), self.dist.world) == self.dist.rank)[0]
+            if own.size == 0:
+                raise ValueError("every rank must own at least one worker")
+            self.gid0, N = int(own[0]), int(own.size)
+            XX = XX[self.gid0 * s:(self.gid0 + N) * s]
+            YY = YY[self.gid0 * s:(self.gid0 + N) * s]
+        self.N, self.d, self.s, self.logistic, self.lam = int(N), int(d), int(s), logistic, float(lam)
+        self.dp = nv.padded(self.d)
         self.X = torch.from_numpy(np.ascontiguousarray(XX.reshape(N, s, d))).to(self.dev)
         self.y = torch.from_numpy(np.ascontiguousarray(YY.reshape(N, s))).to(self.dev)
         G, self.b, self.hyy = LA.gram(self.X, self.y, self.dp)
         self.Gsum = G.sum(0)
+        if self.dist is not None:
+            self.dist.all_reduce_sum_(self.Gsum)      # setup plumbing (NCCL), not on the iteration path
         self.store = nv.STORE_F64 if store in ("f64", nv.STORE_F64) else nv.STORE_F32
         if not logistic:
             self.P = LA.pack_sym(G, self.d, self.store)
@@ -47,6 +64,7 @@ class FirstOrder:
         """Least-squares engine from device-resident pieces (packed Grams ``P`` (N, packed), ``b``
         (N, dp), ``0.5 y'y`` (N,), ``sum_n G_n`` (dp, dp)): the scaled configs never hold X."""
         self = cls.__new__(cls)
+        self.dist, self.Nglob, self.gid0 = None, int(N), 0
         self.dev = device or P.device
         self.N, self.d, self.s, self.logistic, self.lam = int(N), int(d), 0, False, 0.0
         self.dp = nv.padded(self.d)
@@ -163,11 +181,12 @@ class FirstOrder:
         obj_h, loss_h, comm_h, t_h = self._hist(T)
         ctrl = torch.tensor([1, 0, 1 if accuracy is not None else 0, 1], dtype=torch.int64, device=dev)
         cnt = torch.zeros((2,), dtype=torch.int32, device=dev)
-        hm = torch.as_tensor(np.asarray(Hmax, dtype=np.float64), device=dev)
+        hm = torch.as_tensor(np.asarray(Hmax, dtype=np.float64).reshape(-1)[self.gid0:self.gid0 + N]
+                             .copy(), device=dev)
         un = torch.as_tensor(np.asarray(uni if uni is not None else np.zeros(T + 2)), dtype=f64,
                              device=dev)
-        cp = torch.as_tensor(np.asarray(cumprob if cumprob is not None else np.ones(N)), dtype=f64,
-                             device=dev)
+        cp = torch.as_tensor(np.asarray(cumprob if cumprob is not None else np.ones(self.Nglob)),
+                             dtype=f64, device=dev)
         p = nv.GadmmShared()
         p.theta, p.Y, p.fw, p.ghat, p.theta_hat = (theta.data_ptr(), self.Y.data_ptr(),
                                                    self.fw.data_ptr(), ghat.data_ptr(), that.data_ptr())
@@ -178,17 +197,43 @@ class FirstOrder:
         p.step, p.thr, p.obj0 = float(step), float(thr), float(obj0)
         p.acc = float(accuracy) if accuracy is not None else 0.0
         p.N, p.d, p.dp, p.kind, p.max_iter, p.logistic = N, self.d, dp, kind, T, int(self.logistic)
+        W = self.dist.world if self.dist is not None else 1
+        rank = self.dist.rank if self.dist is not None else 0
+        split = W > 1 or N * dp >= 65536
+        row = dp + 64
+        if W > 1:
+            sym = self.dist.symm_bytes(2 * W * row * 8 + 256)
+            xbuf = sym.local[:2 * W * row * 8].view(f64)
+            xflag = sym.local[2 * W * row * 8:2 * W * row * 8 + 2 * W * 8].view(torch.int64)
+            xb_peer = torch.tensor(sym.peer_ptrs, dtype=torch.int64, device=dev)
+            xf_peer = torch.tensor([q + 2 * W * row * 8 for q in sym.peer_ptrs], dtype=torch.int64,
+                                   device=dev)
+        else:
+            sym = None
+            xbuf = torch.zeros((2 * row,), dtype=f64, device=dev)
+            xflag = torch.zeros((2,), dtype=torch.int64, device=dev)
+            xb_peer = torch.tensor([xbuf.data_ptr()], dtype=torch.int64, device=dev)
+            xf_peer = torch.tensor([xflag.data_ptr()], dtype=torch.int64, device=dev)
+        dnpart = torch.zeros((dp // 64,), dtype=f64, device=dev)
+        cnt2 = torch.zeros((2,), dtype=torch.int32, device=dev)
+        p.xbuf, p.xflag, p.xbuf_peer, p.xflag_peer = (xbuf.data_ptr(), xflag.data_ptr(),
+                                                      xb_peer.data_ptr(), xf_peer.data_ptr())
+        p.dnpart, p.counters2 = dnpart.data_ptr(), cnt2.data_ptr()
+        p.Nglob, p.gid0, p.rank, p.nranks, p.split_server = self.Nglob, self.gid0, rank, W, int(split)
         L = nv.lib()
 
         def body():
             self.provider(theta, 0)
             nv.check(L.gadmm_shared_update(C.byref(p), nv.stream_ptr()))
-            self.launches += 1
+            self.launches += 2 if split else 1
 
         self._drive(body, ctrl, T, accuracy is not None, window)
         hit = int(ctrl[1].item())
         n = hit if hit else T
-        keep = (theta, ghat, that, dnorm, hm, un, cp, cnt)   # alive until here
+        if self.dist is not None:
+            self.dist.barrier()
+        keep = (theta, ghat, that, dnorm, hm, un, cp, cnt, sym, xbuf, xflag, xb_peer, xf_peer,
+                dnpart, cnt2)                               # alive until here
         del keep
         return (obj_h[1:n + 1].cpu().numpy(), loss_h[1:n + 1].cpu().numpy(), self._time(t_h, n),
                 comm_h[1:n + 1].cpu().numpy(), theta[:self.d].cpu().numpy())

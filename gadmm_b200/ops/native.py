@@ -104,9 +104,12 @@ class GadmmShared(C.Structure):
         ("theta", _vp), ("Y", _vp), ("fw", _vp), ("ghat", _vp), ("theta_hat", _vp), ("dnorm", _vp),
         ("Hmax", _vp), ("uni", _vp), ("cumprob", _vp), ("obj_hist", _vp), ("loss_hist", _vp),
         ("comm_hist", _vp), ("t_hist", _vp), ("ctrl", _vp), ("counters", _vp),
+        ("xbuf", _vp), ("xflag", _vp), ("xbuf_peer", _vp), ("xflag_peer", _vp), ("dnpart", _vp),
+        ("counters2", _vp),
         ("step", C.c_double), ("thr", C.c_double), ("obj0", C.c_double), ("acc", C.c_double),
         ("N", C.c_int), ("d", C.c_int), ("dp", C.c_int), ("kind", C.c_int), ("max_iter", C.c_int),
-        ("logistic", C.c_int),
+        ("logistic", C.c_int), ("Nglob", C.c_int), ("gid0", C.c_int), ("rank", C.c_int),
+        ("nranks", C.c_int), ("split_server", C.c_int), ("reserved", C.c_int),
     ]
 
 

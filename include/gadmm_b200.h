@@ -185,9 +185,19 @@ typedef struct GadmmShared {      /* shared-iterate methods: GD, LAG-PS, LAG-WK,
   double* comm_hist;              /* comm_iter_final */
   unsigned long long* t_hist;
   unsigned long long* ctrl;       /* [0]=iteration (1-based), [1]=hit, [2]=stop enabled, [3]=comm_iter */
-  unsigned int* counters;         /* [2] ticket, upload flag (zero-initialised) */
+  unsigned int* counters;         /* [2] ticket, uploads of this iteration (zero-initialised) */
+  /* multi-GPU / parallel server (split_server != 0): workers gid0..gid0+N-1 of Nglob live here;
+   * column sums, objective partial and upload count are exchanged through xbuf/xflag (symmetric
+   * memory, P2P stores + release flags); the theta step is replicated on every GPU. */
+  double* xbuf;                   /* [2][nranks][dp+64] */
+  unsigned long long* xflag;      /* [2][nranks] */
+  double* const* xbuf_peer;       /* [nranks] */
+  unsigned long long* const* xflag_peer;
+  double* dnpart;                 /* [dp/64] */
+  unsigned int* counters2;        /* [2] zero-initialised */
   double step, thr, obj0, acc;
   int N, d, dp, kind, max_iter, logistic;
+  int Nglob, gid0, rank, nranks, split_server, reserved;
 } GadmmShared;
 int gadmm_shared_update(const GadmmShared* p, void* stream);
 

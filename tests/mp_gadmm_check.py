@@ -52,6 +52,22 @@ def main():
         assert out[2] == rs[2], (mode, out[2], rs[2])
         np.testing.assert_allclose(out[0], rs[0], rtol=1e-9, atol=1e-9)
         used.append(out[4].nvls)
+    # parameter-server baselines with the workers split over the GPUs (fused P2P reduce + step)
+    rng2 = np.random.default_rng(8)
+    Nb, sb, db = 11, 20, 40
+    Xb = rng2.standard_normal((Nb * sb, db))
+    Yb = Xb @ rng2.standard_normal(db) + 0.1 * rng2.standard_normal(Nb * sb)
+    ob = O.opt_sol_closedForm(Xb, Yb)
+    Xl = [Xb[i * sb:(i + 1) * sb] for i in range(Nb)]
+    yl = [Yb[i * sb:(i + 1) * sb] for i in range(Nb)]
+    Hm = np.array([np.linalg.eigvalsh(x.T @ x)[-1] for x in Xl])
+    argsb = (Xl, yl, Nb, db, Hm, 400, ob, Xb, Yb, sb)
+    ra = O.GD_DGD_LAG(*argsb, rng=3)
+    rb = g.GD_DGD_LAG(*argsb, rng=3, backend="b200", dist=D)
+    for kk in (0, 3, 6, 10, 14, 16):
+        np.testing.assert_allclose(ra[kk], rb[kk], rtol=1e-7, atol=1e-9, err_msg=f"baseline curve {kk}")
+    live = int(np.nonzero(ra[7] < 1e-7)[0][0]) if np.any(ra[7] < 1e-7) else 400
+    np.testing.assert_array_equal(ra[9][:live], rb[9][:live])
     D.barrier()
     if D.rank == 0:
         print(f"STAR_NVLS_USED={used}")
