@@ -86,6 +86,10 @@ find_path_kernel(const double* __restrict__ xy, int N, int model, double area, i
   __shared__ int s_idx[32];
   __shared__ int s_cur;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nw = blockDim.x >> 5;
+  // batched: CTA b builds chain b from xy[b] (d_square / P_central / center only for a single chain)
+  xy += (size_t)blockIdx.x * 2 * N;
+  path += (size_t)blockIdx.x * N;
+  cost += (size_t)blockIdx.x * (N > 1 ? N - 1 : 1);
   for (int i = tid; i < N; i += blockDim.x) {
     px[i] = xy[2 * i];
     py[i] = xy[2 * i + 1];
@@ -192,6 +196,9 @@ int gadmm_philox_normal(void* out, size_t n, int is_f32, unsigned long long seed
   return 0;
 }
 
+int gadmm_find_path_batch(const double* xy, int K, int N, int model, int* path, double* cost,
+                          void* stream);
+
 int gadmm_find_path(const double* xy, int N, int model, int* path, double* cost, double* d_square,
                     double* P_central, int* center, void* stream) {
   GADMM_REQUIRE(N >= 1 && N <= 8192, "find_path: N=%d out of range [1, 8192]", N);
@@ -205,6 +212,22 @@ int gadmm_find_path(const double* xy, int N, int model, int* path, double* cost,
   }
   find_path_kernel<<<1, 1024, smem, (cudaStream_t)stream>>>(xy, N, model, model == 1 ? 250.0 : 50.0,
                                                           path, cost, d_square, P_central, center);
+  GADMM_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+
+/* K chains at once: xy [K][N][2] -> path [K][N] (0-based), cost [K][max(N-1,1)]; one CTA each. */
+int gadmm_find_path_batch(const double* xy, int K, int N, int model, int* path, double* cost,
+                          void* stream) {
+  GADMM_REQUIRE(N >= 1 && N <= 8192 && K >= 1, "find_path_batch: bad N=%d K=%d", N, K);
+  GADMM_REQUIRE(model == 0 || model == 1, "find_path_batch: model must be 0 or 1");
+  const int smem = N * (2 * (int)sizeof(double) + 1) + 16;
+  if (smem > 48 * 1024)
+    GADMM_CUDA_OK(cudaFuncSetAttribute(find_path_kernel,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  find_path_kernel<<<K, 1024, smem, (cudaStream_t)stream>>>(xy, N, model, model == 1 ? 250.0 : 50.0,
+                                                          path, cost, nullptr, nullptr, nullptr);
   GADMM_CUDA_OK(cudaGetLastError());
   return 0;
 }

@@ -312,12 +312,16 @@ class ChainEngine:
         return num_iter
 
     # ------------------------------------------------------- D-GADMM with device-side re-chaining
-    def run_device_rechain(self, num_iter, chain_source, tau, window: int = 32, chunk: int = 256):
+    def run_device_rechain(self, num_iter, chain_source, tau, window: int = 32, chunk: int = 256,
+                           chunk_source=None):
         """D-GADMM without the host in the loop: the chains of the coming windows are uploaded in
         chunks of ``chunk`` rows; two tiny kernels in front of every head kernel switch tables and
         pull the new remote neighbours' theta over NVLink when ``it % tau == 0`` (csrc/rechain.cu).
         ``chain_source(kk)`` returns the 0-based chain of window ``kk`` (kk = 1, 2, ...; called in
-        increasing order).  Returns ``Iter``."""
+        increasing order).  ``chunk_source(base, K)`` (optional) returns a device int32 tensor
+        (K, N) with the chains of windows base..base+K-1 -- e.g. from
+        :func:`gadmm_b200.ops.topology.find_path_batch_device`, which keeps chain generation on
+        the GPU as well.  Returns ``Iter``."""
         assert self.dynamic, "device re-chaining needs both inverses (dynamic=True)"
         num_iter = min(int(num_iter), self.max_iter)
         L = nv.lib()
@@ -364,10 +368,14 @@ class ChainEngine:
         while done < num_iter:
             if tau_i:
                 torch.cuda.current_stream().synchronize()       # previous chunk fully consumed
-                for q in range(K):
-                    paths_host[q] = torch.from_numpy(np.asarray(chain_source(base + q), dtype=np.int32))
                 dyn_host[0], dyn_host[1] = base, K
-                paths_dev.copy_(paths_host, non_blocking=True)
+                if chunk_source is not None:
+                    paths_dev.copy_(chunk_source(base, K))
+                else:
+                    for q in range(K):
+                        paths_host[q] = torch.from_numpy(np.asarray(chain_source(base + q),
+                                                                    dtype=np.int32))
+                    paths_dev.copy_(paths_host, non_blocking=True)
                 dyn.copy_(dyn_host, non_blocking=True)
                 it_star = (base + K) * tau_i if tau_i > 1 else base + K + 1
                 target = min(num_iter, it_star - 1)

@@ -62,7 +62,7 @@ def static_gadmm(XX, YY, rho, no_workers, num_feature, noSamples, num_iter, obj0
 
 
 def _dynamic(XX, YY, rho, N, d, s, num_iter, obj0, acc, first_path, first_cost, tau, next_chain,
-             store, window, dist, return_engine, rechain_mode="device"):
+             store, window, dist, return_engine, rechain_mode="device", device_chain_seed=None):
     """``rechain_mode="device"``: chains are uploaded in chunks and switched by the re-chain kernels
     inside the CUDA graph (no host round trip per window); ``"host"``: tables are rebuilt on the host
     at every re-chain (kept for comparison / debugging)."""
@@ -76,7 +76,23 @@ def _dynamic(XX, YY, rho, N, d, s, num_iter, obj0, acc, first_path, first_cost, 
         cost_at[i] = float(np.sum(pc))
         return np.asarray(p1, dtype=np.int64) - 1
 
-    if rechain_mode == "device":
+    if rechain_mode == "device" and device_chain_seed is not None and tau_i is not None:
+        # chains are drawn and built on the GPU too (Philox positions + one CTA per chain)
+        from ..ops.topology import find_path_batch_device
+        chunks = []
+
+        def chunk_source(base, K):
+            paths, sums = find_path_batch_device(K, N, seed=int(device_chain_seed), stream_id=base,
+                                                 model=1, device=eng.dev)
+            chunks.append((base, sums))
+            return paths
+
+        it = eng.run_device_rechain(num_iter, None, tau, window=window, chunk_source=chunk_source)
+        for base, sums in chunks:
+            for q, v in enumerate(sums.cpu().numpy()):
+                kk = base + q
+                cost_at[kk * tau_i if tau_i > 1 else kk + 1] = float(v)
+    elif rechain_mode == "device":
         def chain_source(kk):
             return rechain(kk * tau_i if tau_i > 1 else kk + 1)
         it = eng.run_device_rechain(num_iter, chain_source, tau, window=window)
@@ -94,9 +110,11 @@ def _dynamic(XX, YY, rho, N, d, s, num_iter, obj0, acc, first_path, first_cost, 
 
 def dynamic_gadmm(XX, YY, rho, no_workers, num_feature, noSamples, num_iter, obj0, acc, path,
                   pathCost, coherence_Time, rng=None, rechain=None, store="f64", window=32,
-                  dist=None, return_engine=False, rechain_mode="device"):
-    """D-GADMM with live ``findPath2`` re-chaining (dynamic_group_ADMM_closedForm.m:18-21).  Chains
-    are drawn on rank 0 and broadcast so that every GPU installs the same tables."""
+                  dist=None, return_engine=False, rechain_mode="device", chain_gen="host"):
+    """D-GADMM with live ``findPath2`` re-chaining (dynamic_group_ADMM_closedForm.m:18-21).
+    ``chain_gen="host"``: chains are drawn with NumPy on rank 0 and broadcast (bit-identical to
+    the oracle for the same ``rng``); ``chain_gen="device"``: positions come from the Philox
+    generator (seed = ``rng``) and the greedy chains are built on the GPU, one CTA per chain."""
     dist = dist or Dist()
     g = np.random.default_rng(rng) if not isinstance(rng, np.random.Generator) else rng
 
@@ -107,9 +125,12 @@ def dynamic_gadmm(XX, YY, rho, no_workers, num_feature, noSamples, num_iter, obj
         out = dist.broadcast_object(out)
         return out[0], out[1]
 
+    seed = None
+    if chain_gen == "device" and rechain is None:
+        seed = int(rng) if isinstance(rng, (int, np.integer)) else 0
     return _dynamic(XX, YY, rho, no_workers, num_feature, noSamples, num_iter, obj0, acc, path,
                     np.sum(pathCost), coherence_Time, next_chain, store, window, dist,
-                    return_engine, rechain_mode)
+                    return_engine, rechain_mode, seed)
 
 
 def dynamic_gadmm_v0(XX, YY, rho, no_workers, num_feature, noSamples, num_iter, obj0, acc,

@@ -300,6 +300,9 @@ int gadmm_philox_normal(void* out, size_t n, int is_f32, unsigned long long seed
  * d_square (optional): N*N, P_central (optional): N, center (optional): 1 int. */
 int gadmm_find_path(const double* xy, int N, int model, int* path, double* cost, double* d_square,
                     double* P_central, int* center, void* stream);
+/* K chains at once (one CTA each): xy [K][N][2] -> path [K][N], cost [K][max(N-1,1)]. */
+int gadmm_find_path_batch(const double* xy, int K, int N, int model, int* path, double* cost,
+                          void* stream);
 
 #ifdef __cplusplus
 }

@@ -35,3 +35,16 @@ def test_philox_fills():
         assert abs(float(z.double().mean())) < 0.01 and abs(float(z.double().std()) - 1.0) < 0.01
         k = float(((z.double()) ** 4).mean())
         assert abs(k - 3.0) < 0.1
+
+
+def test_find_path_batch_matches_single():
+    from gadmm_b200.ops.topology import find_path_batch_device, find_path_device, philox_uniform
+    K, N = 5, 97
+    paths, cost_sums = find_path_batch_device(K, N, seed=21, stream_id=3, model=1)
+    xy = philox_uniform(K * N * 2, seed=21, stream_id=3, scale=250.0).view(K, N, 2)
+    for k in range(K):
+        ref = g.findPath2(N, points=(xy[k, :, 0].cpu().numpy(), xy[k, :, 1].cpu().numpy()))
+        np.testing.assert_array_equal(paths[k].cpu().numpy() + 1, ref[0])
+        assert float(cost_sums[k]) == pytest.approx(ref[1].sum(), rel=1e-14)
+        one = find_path_device(xy[k].contiguous(), 1, want_grid=False)
+        np.testing.assert_array_equal(one[0], ref[0])
