@@ -433,7 +433,7 @@ int gadmm_chain_iterate(const GadmmChain* c, int n_iter, void* stream) {
   return 0;
 }
 
-int gadmm_chain_launches_per_iter(void) { return 3; }   /* 5 with split_finish */
+int gadmm_chain_launches_per_iter(void) { return 3; }   /* +2 finisher launches with split_finish */
 
 int gadmm_chain_configure(void) {
   if (int e = configure_half<double, SymvCfg<double>::STAGES>()) return e;

@@ -125,7 +125,7 @@ class ChainEngine:
         self.ctrl[2] = 1 if self.stop else 0
 
     # ------------------------------------------------------------------------------- setup
-    def ingest_host(self, XX, YY, s: int, end_workers=(None,), batch: int = 0):
+    def ingest_host(self, XX, YY, s: int, batch: int = 0):
         """Upload the local workers' shards, build Gram / RHS / inverses on the GPU."""
         XX = np.asarray(XX, dtype=np.float64)
         YY = np.asarray(YY, dtype=np.float64).reshape(-1)

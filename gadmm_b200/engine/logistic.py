@@ -112,7 +112,7 @@ def logreg_gd_single(X, Y, x, C1, C2, term1, term2, lambda_logistic, gdStep, **k
 
 def gadmm_logistic_newton(XX, YY, rho, no_workers, num_feature, per_samples, num_iter, obj0,
                           lambda_logistic, acc, newton_tol=1e-10, max_newton=30, faithful=False,
-                          naive=True, return_state=False):
+                          naive=True, return_state=False, hessian_tc_min_d=128):
     """``group_ADMM_logistic`` with exact local solves by damped Newton on the GPU."""
     st = _LogisticState(XX, YY, no_workers, num_feature, per_samples, lambda_logistic)
     N, d, dp, dev = st.N, st.d, st.dp, st.dev
@@ -158,9 +158,15 @@ def gadmm_logistic_newton(XX, YY, rho, no_workers, num_feature, per_samples, num
                 live = gn > newton_tol * torch.clamp(x.norm(dim=1), min=1.0)
                 if not bool(live.any().item()):
                     break
-                w = st.wout[act]
-                Xw = Xa * torch.sqrt(w).unsqueeze(2)
-                H, _, _ = LA.gram(Xw, torch.zeros_like(w), dp)
+                w = st.wout[act].contiguous()
+                if d >= hessian_tc_min_d:
+                    # X'DX on the tensor cores: the row scaling by sqrt(D) is fused into the
+                    # split/transpose pass of the tcgen05 Gram (fp32-grade Hessian; Newton with an
+                    # inexact Hessian still converges, the gradient stays fp64)
+                    H = LA.gram_tc(Xa, dp, w=w)
+                else:
+                    Xw = Xa * torch.sqrt(w).unsqueeze(2)
+                    H, _, _ = LA.gram(Xw, torch.zeros_like(w), dp)
                 H += cr.unsqueeze(2) * eye
                 Hinv = LA.shifted_inverse(H, d, st.lam_log)
                 step = LA.BatchedSymv(LA.pack_sym(Hinv, d), dp)(g.contiguous())

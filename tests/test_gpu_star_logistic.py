@@ -60,3 +60,17 @@ def test_logistic_newton_matches_oracle(small_logistic):
     b = g.group_ADMM_logistic(*args, backend="b200")
     assert a[2] == b[2] and a[2] < 100
     np.testing.assert_allclose(a[0], b[0], rtol=1e-7)
+
+
+def test_logistic_newton_tensor_core_hessian():
+    """d=160 -> the Hessian X'DX goes through the tcgen05 Gram; iterates still match the oracle."""
+    rng = np.random.default_rng(12)
+    N, s, d, lam = 4, 200, 160, 1e-2
+    XX = rng.standard_normal((N * s, d)) / np.sqrt(d)
+    YY = np.where(XX @ rng.standard_normal(d) + 0.3 * rng.standard_normal(N * s) > 0, 1.0, -1.0)
+    star = O.opt_sol_logistic(XX, YY, d, lam, N)
+    args = (XX, YY, 0.5, N, d, s, 60, star, lam, 1e-5)
+    a = O.group_ADMM_logistic(*args)
+    b = g.group_ADMM_logistic(*args, backend="b200")
+    assert a[2] == b[2]
+    np.testing.assert_allclose(a[0], b[0], rtol=1e-7)
