@@ -104,8 +104,10 @@ def gadmm_logistic_gd(XX, YY, rho, no_workers, num_feature, per_samples, num_ite
 
 
 def logreg_gd_single(X, Y, x, C1, C2, term1, term2, lambda_logistic, gdStep, **kw):
-    """``logReg_GD`` for one worker through the same kernel (N=1 chain: the linear term enters as
-    an edge dual of a fictitious... ) -- kept on the oracle: a single 50x50 solve is launch-bound."""
+    """``logReg_GD`` for one worker with caller-supplied linear terms.  The GPU kernel
+    (``logistic_half_gd_kernel``) derives those terms from the chain state itself, so this
+    stand-alone helper (a single 50x50 solve, launch-bound on a GPU) evaluates on the host with the
+    oracle's implementation; the batched in-chain solve is :func:`gadmm_logistic_gd`."""
     from ..oracle import logReg_GD
     return logReg_GD(X, Y, x, C1, C2, term1, term2, lambda_logistic, gdStep, **kw)
 
