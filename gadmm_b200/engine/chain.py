@@ -123,6 +123,9 @@ class ChainEngine:
             self.P_end = {}   # local index -> (1, pe) tensor for chain-end workers (c=1)
         self.ctrl[0] = 1
         self.ctrl[2] = 1 if self.stop else 0
+        self.ctrl[3] = -1          # first-crossing register of the persistent kernel (= ~0)
+        self.objring = torch.zeros((32 * Nloc,), dtype=f64, device=dev)
+        self.ringcnt = torch.zeros((32,), dtype=i32, device=dev)
 
     # ------------------------------------------------------------------------------- setup
     def ingest_host(self, XX, YY, s: int, batch: int = 0):
@@ -293,6 +296,8 @@ class ChainEngine:
         num_iter = self.max_iter if num_iter is None else min(int(num_iter), self.max_iter)
         nv.lib().gadmm_chain_configure()
         done = getattr(self, "_resume_from", 0)
+        if rechain is None and self.persistent_ok():
+            return self._run_persistent(num_iter, done)
         while done < num_iter:
             it_next = done + 1
             if rechain is not None and coherence is not None and it_next > 1 \
@@ -424,6 +429,30 @@ class ChainEngine:
 
     step_d2h_bytes = 16
 
+    # ------------------------------------------------------ persistent kernel (small problems)
+    def persistent_ok(self) -> bool:
+        if os.environ.get("GADMM_B200_NO_PERSISTENT") == "1" or self.path0 is None:
+            return False
+        return nv.lib().gadmm_chain_persistent_supported(C.byref(self.desc())) == 0
+
+    def _run_persistent(self, num_iter: int, done: int, window: int = 4096) -> int:
+        """Reference-size problems: the whole solve is one cooperative launch per ``window``
+        iterations (csrc/gadmm_persistent.cu); state stays in shared memory."""
+        L = nv.lib()
+        c = self.desc()
+        while done < num_iter:
+            n = min(window, num_iter - done)
+            nv.check(L.gadmm_chain_persistent(C.byref(c), int(n), nv.ptr(self.objring),
+                                              nv.ptr(self.ringcnt), nv.stream_ptr()))
+            self.launches += 1
+            done += n
+            if self.stop:
+                hit = int(self.ctrl[1].item())
+                if hit:
+                    return hit
+        torch.cuda.synchronize(self.dev)
+        return num_iter
+
     # ----------------------------------------------------------------------------- results
     def results(self, Iter: int):
         torch.cuda.synchronize(self.dev)
@@ -480,6 +509,7 @@ class ChainEngine:
             self.loss_hist[1:n + 1] = torch.as_tensor(np.asarray(st["loss"][:n]), device=self.dev)
         self.ctrl[0] = it + 1
         self.ctrl[1] = 0
+        self.ctrl[3] = -1
         self._resume_from = it
         if st.get("path") is not None and self.path0 is None:
             self.set_path(np.asarray(st["path"], dtype=np.int64) - 1)

@@ -132,6 +132,14 @@ int gadmm_chain_configure(void);
 /* Number of kernel launches gadmm_chain_iterate issues per iteration. */
 int gadmm_chain_launches_per_iter(void);
 
+/* Persistent single-launch variant for small problems (one GPU, fp64 tiles, dp <= 128, one CTA
+ * per worker co-resident; cooperative launch).  The whole state lives in shared memory, phase
+ * ordering is by neighbour flags, a grid barrier every 8 iterations agrees on the stop decision.
+ * objring: 32*Nloc doubles, ringcnt: 32 uint32 (zero-initialised); ctrl[3] = ~0 before first use. */
+int gadmm_chain_persistent_supported(const GadmmChain* c);
+int gadmm_chain_persistent(const GadmmChain* c, int n_iter, double* objring, unsigned int* ringcnt,
+                           void* stream);
+
 /* ---- D-GADMM re-chaining on the device (K10; dynamic_group_ADMM_closedForm.m:18-21) -----------
  * Launched once per iteration in front of the head kernel; a no-op unless
  * it > 1 && it % tau == 0.  Window index kk = it/tau - (tau==1) - dyn[0] selects paths[kk]. */

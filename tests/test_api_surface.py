@@ -1,0 +1,75 @@
+"""CPU-side guard: every public entry point resolves to an engine function whose signature accepts
+the reference's positional arguments (catches wiring mistakes without a GPU)."""
+import inspect
+
+import gadmm_b200 as g
+from gadmm_b200 import engine
+
+
+REF_ARITY = {   # public name -> (engine function, number of positional args of the .m signature)
+    "group_ADMM_closedForm": ("gadmm_closed_form", 9),
+    "static_group_ADMM_closedForm": ("static_gadmm", 11),
+    "dynamic_group_ADMM_closedForm": ("dynamic_gadmm", 12),
+    "dynamic_group_ADMM_closedForm_v0": ("dynamic_gadmm_v0", 12),
+    "group_ADMM_logistic": ("gadmm_logistic_newton", 10),
+    "group_ADMM_logistic_GD": ("gadmm_logistic_gd", 11),
+    "standared_ADMM": ("star_admm", 9),
+    "GD_DGD_LAG": ("gd_dgd_lag", 10),
+    "GD_DGD_LAG_logistic": ("gd_dgd_lag_logistic", 11),
+    "dual_averaging": ("dual_averaging", 9),
+    "dual_averaging_logisticReg": ("dual_averaging_logistic", 10),
+    "opt_sol_closedForm": ("opt_sol_closed_form", 2),
+}
+
+
+def test_public_names_and_engine_targets():
+    for name, (target, arity) in REF_ARITY.items():
+        assert hasattr(g, name), name
+        fn = getattr(engine, target)
+        inspect.signature(fn).bind(*range(arity))
+        # the public wrapper takes the same positional arguments plus backend=
+        sig = inspect.signature(getattr(g, name))
+        sig.bind(*range(arity), backend="oracle")
+    for name in ("findPath", "findPath2", "calc_cost", "opt_sol", "opt_sol_logistic", "logReg_GD",
+                 "group_ADMM", "standard_ADMM"):
+        assert callable(getattr(g, name))
+
+
+def test_engine_classes_expose_their_run_paths():
+    from gadmm_b200.engine.chain import ChainEngine
+    from gadmm_b200.engine.first_order import FirstOrder
+    from gadmm_b200.engine.star import StarEngine
+    for cls, names in ((ChainEngine, ("ingest_host", "ingest_gram", "set_path", "iterate", "run",
+                                      "run_device_rechain", "persistent_ok", "_run_persistent", "step",
+                                      "results", "state", "load_state")),
+                       (FirstOrder, ("from_parts", "lambda_max", "hmax_per_worker", "provider",
+                                     "run_shared", "run_dgd", "run_dualavg")),
+                       (StarEngine, ("iterate", "run", "results"))):
+        for n in names:
+            assert hasattr(cls, n), (cls.__name__, n)
+
+
+def test_ctypes_mirrors_match_header_sizes():
+    """sizeof of every ctypes mirror equals the C struct size computed from the header layout
+    (pointers/doubles/long longs are 8 bytes, ints 4, no padding holes by construction)."""
+    import ctypes
+    import re
+    from gadmm_b200.ops import native as nv
+    hdr = open(__file__.replace("tests/test_api_surface.py", "include/gadmm_b200.h")).read()
+    for name in ("GadmmChain", "GadmmRechain", "GadmmStar", "GadmmShared", "GadmmOwn", "GadmmLogistic"):
+        body = re.search(r"typedef struct %s \{(.*?)\} %s;" % (name, name), hdr, re.S).group(1)
+        body = re.sub(r"/\*.*?\*/", "", body, flags=re.S)
+        size = 0
+        for decl in body.split(";"):
+            decl = decl.strip()
+            if not decl:
+                continue
+            n = decl.count(",") + 1
+            if "*" in decl or decl.startswith(("double", "long long", "unsigned long long")):
+                size += 8 * n
+            elif decl.startswith(("int", "unsigned int")):
+                size += 4 * n
+            else:
+                raise AssertionError(f"unparsed member in {name}: {decl!r}")
+        size = (size + 7) // 8 * 8
+        assert ctypes.sizeof(getattr(nv, name)) == size, (name, ctypes.sizeof(getattr(nv, name)), size)
