@@ -278,15 +278,20 @@ class ChainEngine:
         if not use_graph or n_iter < 4:
             nv.check(L.gadmm_chain_iterate(C.byref(c), int(n_iter), nv.stream_ptr()))
         else:
-            g = self._graphs.get(n_iter)
-            if g is None:
-                torch.cuda.synchronize(self.dev)
-                g = torch.cuda.CUDAGraph()
-                with torch.cuda.graph(g):
-                    nv.check(L.gadmm_chain_iterate(C.byref(c), int(n_iter), nv.stream_ptr()))
-                self._graphs[n_iter] = g    # capture does not execute; replay below does
-            g.replay()
+            self._capture(n_iter).replay()
         self.launches += (5 if self.split_finish else 3) * int(n_iter)
+
+    def _capture(self, n_iter: int):
+        g = self._graphs.get(n_iter)
+        if g is None:
+            nv.lib().gadmm_chain_configure()
+            c = self.desc()
+            torch.cuda.synchronize(self.dev)
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                nv.check(nv.lib().gadmm_chain_iterate(C.byref(c), int(n_iter), nv.stream_ptr()))
+            self._graphs[n_iter] = g        # capture does not execute anything
+        return g
 
     def run(self, num_iter: Optional[int] = None, window: int = 32, rechain=None,
             coherence: Optional[float] = None, use_graph: bool = True) -> int:
@@ -298,6 +303,8 @@ class ChainEngine:
         done = getattr(self, "_resume_from", 0)
         if rechain is None and self.persistent_ok():
             return self._run_persistent(num_iter, done)
+        if use_graph and rechain is None and num_iter - done >= max(4, window):
+            self._capture(window)              # capture before the device clock of iteration 1
         while done < num_iter:
             it_next = done + 1
             if rechain is not None and coherence is not None and it_next > 1 \

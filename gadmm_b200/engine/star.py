@@ -105,31 +105,35 @@ class StarEngine:
         D.barrier()
 
     def iterate(self, n, use_graph=True):
-        L = nv.lib()
         if use_graph and n >= 8:
-            g = self._graphs.get(n)
-            if g is None:
-                # first launch outside capture sets the kernel attributes
-                torch.cuda.synchronize(self.dev)
-                g = torch.cuda.CUDAGraph()
-                with torch.cuda.graph(g):
-                    nv.check(L.gadmm_star_iterate(C.byref(self.p), int(n), nv.stream_ptr()))
-                self._graphs[n] = g
-            g.replay()
+            self._graph(n).replay()
         else:
-            nv.check(L.gadmm_star_iterate(C.byref(self.p), int(n), nv.stream_ptr()))
+            nv.check(nv.lib().gadmm_star_iterate(C.byref(self.p), int(n), nv.stream_ptr()))
         self.launches += 2 * n
+
+    def _graph(self, n):
+        g = self._graphs.get(n)
+        if g is None:
+            L = nv.lib()
+            nv.check(L.gadmm_star_iterate(C.byref(self.p), 0, nv.stream_ptr()))   # attributes only
+            torch.cuda.synchronize(self.dev)
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                nv.check(L.gadmm_star_iterate(C.byref(self.p), int(n), nv.stream_ptr()))
+            self._graphs[n] = g
+        return g
 
     def run(self, num_iter=None, window=64):
         T = self.max_iter if num_iter is None else min(int(num_iter), self.max_iter)
-        self.iterate(1, use_graph=False)
-        done = 1
+        if T >= 8:
+            self._graph(min(window, T))        # capture before the clock starts
+        done = 0
         while done < T:
-            if self.stop and int(self.ctrl[1].item()):
-                break
             n = min(window, T - done)
             self.iterate(n)
             done += n
+            if self.stop and int(self.ctrl[1].item()):
+                break
         torch.cuda.synchronize(self.dev)
         hit = int(self.ctrl[1].item())
         return hit if hit else T
