@@ -81,7 +81,10 @@ gadmm_half_iter_kernel(const GadmmChain c, const int color) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   SymvSmem<T, NSTAGES>& sm = *reinterpret_cast<SymvSmem<T, NSTAGES>*>(smem_raw);
   const int nT = c.dp / kT, npairs = (nT + 1) / 2, nsp = c.nsplit;
-  const int k = blockIdx.x / (npairs * nsp), p = (blockIdx.x / nsp) % npairs, part = blockIdx.x % nsp;
+  // `order` puts workers with a neighbour on another GPU first: their theta is published early in
+  // the phase and the peer's dependent CTAs (scheduled first there, too) do not sit spinning
+  const int k = c.order[blockIdx.x / (npairs * nsp)], p = (blockIdx.x / nsp) % npairs,
+            part = blockIdx.x % nsp;
   if (c.color[k] != color) return;
   const unsigned long long it = c.ctrl[0];
   if (c.ctrl[2] != 0ull && c.ctrl[1] != 0ull) return;   // converged: freeze the state
@@ -163,7 +166,7 @@ __global__ void __launch_bounds__(64)
 gadmm_finish_kernel(const GadmmChain c, const int color) {
   __shared__ double red[8];
   __shared__ unsigned int ticket;
-  const int J = blockIdx.x, k = blockIdx.y, tid = threadIdx.x;
+  const int J = blockIdx.x, k = c.order[blockIdx.y], tid = threadIdx.x;
   if (c.color[k] != color) return;
   const unsigned long long it = c.ctrl[0];
   if (c.ctrl[2] != 0ull && c.ctrl[1] != 0ull) return;
@@ -235,7 +238,7 @@ gadmm_dual_objective_kernel(const GadmmChain c) {
   const unsigned long long it = c.ctrl[0];
   if (c.ctrl[2] != 0ull && c.ctrl[1] != 0ull) return;
   if (it > (unsigned long long)c.max_iter) return;
-  const int k = blockIdx.x;
+  const int k = c.order[blockIdx.x];
   const int g = c.gid[k], l = c.left[k], r = c.right[k];
   if (threadIdx.x == 0) {
     if (c.pdl) wait_flag_ge(c.flags + g, it);          // own finisher (tail phase may be running)

@@ -110,6 +110,7 @@ class ChainEngine:
         self.tab_host = torch.zeros((7, Nloc), dtype=i32).pin_memory()
         self.tab_host[0] = torch.from_numpy(self.gids)
         self.owner = torch.from_numpy(self.owner_np).to(dev)
+        self.order = torch.arange(Nloc, dtype=i32, device=dev)
         self.Mptr = torch.zeros((Nloc,), dtype=i64, device=dev)
         self.Mptr_host = torch.zeros((Nloc,), dtype=i64).pin_memory()
         pe = nv.packed_elems(dp)
@@ -210,6 +211,10 @@ class ChainEngine:
                 mp[k] = self.P_end[k].data_ptr()
         self.tab.copy_(th, non_blocking=True)
         self.Mptr.copy_(mp, non_blocking=True)
+        # launch order: workers that exchange theta with another GPU go first in every phase
+        remote = (push[0] >= 0) | (push[1] >= 0)
+        order = np.concatenate([np.nonzero(remote)[0], np.nonzero(~remote)[0]]).astype(np.int32)
+        self.order.copy_(torch.from_numpy(order))
         prev = self.path0
         self.path0 = path0
         self.left, self.right = left, right
@@ -265,6 +270,7 @@ class ChainEngine:
         c.pdl = int(self.pdl)
         c.split_finish = int(self.split_finish)
         c.nsplit = int(self.nsplit)
+        c.order = self.order.data_ptr()
         c.wready, c.sblk, c.fin_counters = (self.wready.data_ptr(), self.sblk.data_ptr(),
                                             self.fin_counters.data_ptr())
         self._desc = c

@@ -36,7 +36,7 @@ class GadmmChain(C.Structure):
         ("d", C.c_int), ("dp", C.c_int), ("Nglob", C.c_int), ("Nloc", C.c_int), ("rank", C.c_int),
         ("nranks", C.c_int), ("store", C.c_int), ("max_iter", C.c_int), ("pdl", C.c_int),
         ("split_finish", C.c_int), ("wready", _vp), ("sblk", _vp), ("fin_counters", _vp),
-        ("nsplit", C.c_int), ("reserved", C.c_int),
+        ("nsplit", C.c_int), ("reserved", C.c_int), ("order", _vp),
     ]
 
 

@@ -121,6 +121,8 @@ typedef struct GadmmChain {
   int nsplit;                /* >= 1: CTAs per pair of tile-rows (tile columns divided into nsplit
                                 ranges); rowpart is then [Nloc][nsplit][dp] */
   int reserved;
+  const int* order;          /* [Nloc] permutation of the local workers: launch order of their CTAs
+                                (workers with a neighbour on another GPU first) */
 } GadmmChain;
 
 int gadmm_chain_half_iter(const GadmmChain* c, int color, void* stream);
