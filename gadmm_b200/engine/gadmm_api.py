@@ -11,12 +11,25 @@ from .chain import ChainEngine
 
 def _engine(XX, YY, rho, N, d, s, num_iter, obj0, acc, dynamic, store="f64", dist=None,
             theta0=None):
+    if dist is None and not dynamic and _small_enough(N, d):
+        from ..parallel.runtime import SoloDist
+        dist = SoloDist()      # tiny problem: every rank runs the persistent single-GPU kernel
     eng = ChainEngine(N, d, rho, obj0, acc, num_iter, dist=dist or Dist(), store=store,
                       dynamic=dynamic)
     eng.ingest_host(XX, YY, s)
     if theta0 is not None:
         eng.set_theta(theta0)
     return eng
+
+
+def _small_enough(N, d) -> bool:
+    """Problems the persistent kernel can hold (one CTA per worker, dp <= 128)."""
+    import torch
+    try:
+        sms = torch.cuda.get_device_properties(torch.cuda.current_device()).multi_processor_count
+    except Exception:
+        return False
+    return N <= sms and (d + 63) // 64 * 64 <= 128
 
 
 def _energy(cost_of_iter, Iter):

@@ -116,3 +116,16 @@ class Dist:
         box = [obj]
         dist.broadcast_object_list(box, src=src)
         return box[0]
+
+
+class SoloDist(Dist):
+    """A world-of-one view on this process's GPU, used under torchrun for problems so small that
+    splitting them over GPUs only adds NVLink latency: every rank then solves the whole problem
+    with the single-GPU persistent kernel (identical results everywhere, no communication)."""
+
+    def __init__(self, device: Optional[torch.device] = None):
+        _, world, local = env_rank_world()
+        self.rank, self.world, self.local_rank = 0, 1, local
+        self.device = device or torch.device("cuda", local if world > 1 else torch.cuda.current_device())
+        if world > 1:
+            torch.cuda.set_device(self.device)

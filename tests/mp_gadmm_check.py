@@ -25,6 +25,14 @@ def main():
     b = g.group_ADMM_closedForm(*base, backend="b200", dist=D)
     assert a[2] == b[2], (a[2], b[2])
     np.testing.assert_allclose(a[0], b[0], rtol=1e-9, atol=1e-9)
+    # tiny problem without an explicit dist: every rank solves it with the persistent kernel
+    rs_ = np.random.default_rng(3)
+    Xs_, Ys_ = rs_.standard_normal((6 * 15, 20)), rs_.standard_normal(6 * 15)
+    os_ = O.opt_sol_closedForm(Xs_, Ys_)
+    a = O.group_ADMM_closedForm(Xs_, Ys_, 2.0, 6, 20, 15, 500, os_, 1e-6)
+    b = g.group_ADMM_closedForm(Xs_, Ys_, 2.0, 6, 20, 15, 500, os_, 1e-6, backend="b200")
+    assert a[2] == b[2], ("solo", a[2], b[2])
+    np.testing.assert_allclose(a[0], b[0], rtol=1e-9, atol=1e-9)
     # dynamic chains: neighbours land on arbitrary GPUs, re-chained every 3 iterations
     prng = np.random.default_rng(0)
     paths, costs = [], []
