@@ -317,6 +317,47 @@ shared_server_kernel(const GadmmShared p) {
   }
 }
 
+// ------------------------------------------------------ chain halo + objective exchange (K8)
+// grid = 3 CTAs.  CTA 0: this GPU's objective partial -> every GPU's fx ring (P2P stores + release
+// flag), wait for all ranks, total -> ftot[it & 1] (same order everywhere -> same stop decision).
+// CTA 1 / CTA 2 (push_y): first / last local gradient row -> the left / right neighbour GPU's Ytab.
+__global__ void __launch_bounds__(256)
+own_exchange_kernel(const GadmmOwn p, const int push_y) {
+  __shared__ double red[32];
+  const unsigned long long it = p.ctrl[0];
+  if (p.ctrl[2] != 0ull && p.ctrl[1] != 0ull) return;
+  const int tid = threadIdx.x, dp = p.dp;
+  if (blockIdx.x == 0) {
+    double f = 0.0;
+    for (int i = tid; i < p.N; i += 256) f += __ldcg(p.fw + i);
+    f = block_sum(f, red);
+    if (tid == 0) {
+      const size_t ring = (size_t)(it & 1ull) * p.nranks;
+      for (int q = 0; q < p.nranks; ++q) p.fx_peer[q][ring + p.rank] = f;
+      __threadfence_system();
+      for (int q = 0; q < p.nranks; ++q) st_release_sys(p.fxflag_peer[q] + ring + p.rank, it);
+      double tot = 0.0;
+      for (int q = 0; q < p.nranks; ++q) {
+        wait_flag_ge(p.fxflag + ring + q, it);
+        tot += *reinterpret_cast<volatile double*>(p.fx + ring + q);
+      }
+      p.ftot[it & 1ull] = tot;
+    }
+    return;
+  }
+  if (!push_y) return;
+  const bool left = blockIdx.x == 1;
+  const int gsrc = left ? p.gid0 : p.gid0 + p.N - 1;     // global row to publish
+  const int peer = left ? p.rank - 1 : p.rank + 1;
+  if (peer < 0 || peer >= p.nranks) return;
+  const double* src = p.Ytab + (size_t)gsrc * dp;
+  double* dst = p.Ytab_peer[peer] + (size_t)gsrc * dp;
+  for (int j = tid; j < dp; j += 256) dst[j] = src[j];
+  __threadfence_system();
+  __syncthreads();
+  if (tid == 0) st_release_sys(p.rowflag_peer[peer] + gsrc, it);
+}
+
 // -------------------------------------------------------------------------- DGD update (K8)
 // theta_n -= step * mean(g over {n, n+-1})  (1/2 at the ends, 1/3 inside), g = ones at
 // iteration 1 (GD_DGD_LAG.m:129-180).  The objective is the one *before* the update (fw).
@@ -328,14 +369,21 @@ dgd_update_kernel(const GadmmOwn p) {
   if (p.ctrl[2] != 0ull && p.ctrl[1] != 0ull) return;
   if (it > (unsigned long long)p.max_iter) return;
   const int n = blockIdx.x, tid = threadIdx.x, dp = p.dp;
+  const int gn = p.gid0 + n, NG = p.Nglob;                 // global position on the chain
+  if (p.nranks > 1 && it > 1ull && tid == 0) {             // halo rows pushed by the neighbour GPUs
+    if (n == 0 && gn > 0) wait_flag_ge(p.rowflag + gn - 1, it);
+    if (n == p.N - 1 && gn < NG - 1) wait_flag_ge(p.rowflag + gn + 1, it);
+  }
+  __syncthreads();
+  const double* Yg = p.Ytab + (size_t)gn * dp;             // == p.Y + n*dp
   for (int j = tid; j < p.d; j += 256) {
     double avg = 1.0;
     if (it > 1ull) {
-      const double g = p.Y[(size_t)n * dp + j];
-      if (p.N == 1) avg = g;
-      else if (n == 0) avg = 0.5 * (g + p.Y[(size_t)(n + 1) * dp + j]);
-      else if (n == p.N - 1) avg = 0.5 * (g + p.Y[(size_t)(n - 1) * dp + j]);
-      else avg = (g + p.Y[(size_t)(n + 1) * dp + j] + p.Y[(size_t)(n - 1) * dp + j]) / 3.0;
+      const double g = Yg[j];
+      if (NG == 1) avg = g;
+      else if (gn == 0) avg = 0.5 * (g + __ldcg(Yg + dp + j));
+      else if (gn == NG - 1) avg = 0.5 * (g + __ldcg(Yg - dp + j));
+      else avg = (g + __ldcg(Yg + dp + j) + __ldcg(Yg - dp + j)) / 3.0;
     }
     p.Theta[(size_t)n * dp + j] -= p.step * avg;
   }
@@ -348,6 +396,7 @@ dgd_update_kernel(const GadmmOwn p) {
   for (int i = tid; i < p.N; i += 256) f += __ldcg(p.fw + i);
   f = block_sum(f, red);
   if (tid == 0) {
+    if (p.nranks > 1) f = p.ftot[it & 1ull];
     const double loss = fabs(f - p.obj0);
     p.obj_hist[it] = f;
     p.loss_hist[it] = loss;
@@ -372,42 +421,68 @@ dualavg_update_kernel(const GadmmOwn p, const int update) {
   __shared__ int s_stop;
   const unsigned long long it = p.ctrl[0];
   if (p.ctrl[2] != 0ull && p.ctrl[1] != 0ull) return;
-  const int tid = threadIdx.x, dp = p.dp, N = p.N;
+  const int tid = threadIdx.x, dp = p.dp, N = p.N, NG = p.Nglob, g0 = p.gid0;
   double f = 0.0;
   for (int i = tid; i < N; i += 256) f += __ldcg(p.fw + i);
   f = block_sum(f, red);                       // identical in every CTA (same order)
+  if (p.nranks > 1) f = p.ftot[it & 1ull];     // all-rank objective from own_exchange_kernel
   const double loss = fabs(f - p.obj0);
   if (tid == 0) s_stop = (it > 1ull && loss < p.acc && p.ctrl[2] != 0ull) ? 1 : 0;
   __syncthreads();
   const bool run = update && !s_stop && it <= (unsigned long long)p.max_iter;
+  // halo rows of Z: left neighbour's last worker (new value in Gauss-Seidel order, old in Jacobi),
+  // right neighbour's first worker (always the previous iterate)
+  const bool haloL = p.nranks > 1 && g0 > 0, haloR = p.nranks > 1 && g0 + N < NG;
+  const unsigned long long vL = p.jacobi ? it - 1ull : it, vR = it - 1ull;
+  if (run && tid == 0) {
+    if (haloL) wait_flag_ge(p.rowflag + NG + g0 - 1, vL);
+    if (haloR) wait_flag_ge(p.rowflag + NG + g0 + N, vR);
+  }
+  __syncthreads();
   if (run) {
     const int j = blockIdx.x * 256 + tid;
     if (j < p.d) {
-      double left_new = 0.0, left_old = 0.0;
+      const double* ZL = p.Ztab + ((size_t)(vL & 1ull) * NG + (g0 - 1)) * dp;
+      const double* ZR = p.Ztab + ((size_t)(vR & 1ull) * NG + (g0 + N)) * dp;
+      double left_new = haloL ? __ldcg(ZL + j) : 0.0, left_old = left_new;
+      double z_first = 0.0, z_last = 0.0;
       for (int n = 0; n < N; ++n) {
         const size_t o = (size_t)n * dp + j;
+        const int gn = g0 + n;
         const double zo = p.Z[o];
         const double lft = p.jacobi ? left_old : left_new;
+        const double rgt = (n == N - 1) ? (haloR ? __ldcg(ZR + j) : 0.0) : p.Z[o + dp];
         double z;
-        if (N == 1) z = 0.0;
-        else if (n == 0) z = p.Z[o + dp];
-        else if (n == N - 1) z = lft;
-        else z = 0.5 * p.Z[o + dp] + 0.5 * lft;
+        if (NG == 1) z = 0.0;
+        else if (gn == 0) z = rgt;
+        else if (gn == NG - 1) z = lft;
+        else z = 0.5 * rgt + 0.5 * lft;
         z += p.Y[o];
         p.Theta[o] = -p.step * z;
         p.Z[o] = z;
         left_new = z;
         left_old = zo;
+        if (n == 0) z_first = z;
+        z_last = z;
       }
+      // publish the boundary rows (version it) into the neighbour GPUs' halo tables
+      const size_t so = (size_t)(it & 1ull) * NG;
+      if (haloL) p.Ztab_peer[p.rank - 1][(so + g0) * dp + j] = z_first;
+      if (haloR) p.Ztab_peer[p.rank + 1][(so + g0 + N - 1) * dp + j] = z_last;
     }
   }
-  __threadfence();
+  __threadfence_system();
   __syncthreads();
   if (tid == 0) ticket = atomicAdd(p.counters, 1u);
   __syncthreads();
   if (ticket != gridDim.x - 1) return;
   if (tid == 0) {
     p.counters[0] = 0u;
+    if (run) {
+      __threadfence_system();
+      if (haloL) st_release_sys(p.rowflag_peer[p.rank - 1] + NG + g0, it);
+      if (haloR) st_release_sys(p.rowflag_peer[p.rank + 1] + NG + g0 + N - 1, it);
+    }
     if (it > 1ull) {                            // close iteration it-1
       p.obj_hist[it - 1] = f;
       p.loss_hist[it - 1] = loss;
@@ -472,6 +547,14 @@ int gadmm_shared_update(const GadmmShared* p, void* stream) {
   shared_update_kernel<<<p->N, 256, 0, (cudaStream_t)stream>>>(*p);
   if (p->split_server)
     shared_server_kernel<<<p->dp / 64, 256, 0, (cudaStream_t)stream>>>(*p);
+  GADMM_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+int gadmm_own_exchange(const GadmmOwn* p, int push_y, void* stream) {
+  GADMM_REQUIRE(p && p->N > 0, "own_exchange: N must be positive");
+  if (p->nranks <= 1) return 0;
+  own_exchange_kernel<<<3, 256, 0, (cudaStream_t)stream>>>(*p, push_y);
   GADMM_CUDA_OK(cudaGetLastError());
   return 0;
 }

@@ -43,12 +43,12 @@ def gd_dgd_lag(X, y, num_workers, num_feature, Hmax, num_iter, obj0, X_fede, y_f
                rng=None, store="f64", dist=None):
     """GPU ``GD_DGD_LAG`` (19 outputs, GD_DGD_LAG.m:1-4).  Under torchrun the parameter-server
     methods (GD, LAG-PS, LAG-WK, IAG) split the workers over the GPUs and reduce inside the server
-    kernel through NVLink peer stores; DGD runs replicated on every GPU."""
+    kernel through NVLink peer stores; DGD exchanges the boundary gradient rows of its chain
+    segments the same way."""
     N, d, T = int(num_workers), int(num_feature), int(num_iter)
     dist = _dist_or_none(dist)
     fo = FirstOrder(X_fede, y_fede, N, d, num_sample, logistic=False, store=store, dist=dist)
-    fo_own = FirstOrder(X_fede, y_fede, N, d, num_sample, logistic=False, store=store) \
-        if dist is not None else None
+    fo_own = None       # DGD shares the distributed engine (chain halos over NVLink)
     Hmax = np.asarray(Hmax, dtype=np.float64).reshape(-1)[:N]
     alpha = 1.0 / fo.lambda_max()                              # :19,46
     gd = fo.run_shared(nv.FO_GD, alpha, 0.0, Hmax, T, obj0, None)
@@ -63,8 +63,7 @@ def gd_dgd_lag_logistic(X, y, num_workers, num_feature, Hmax, num_iter, X_fede, 
     N, d, T = int(num_workers), int(num_feature), int(num_iter)
     dist = _dist_or_none(dist)
     fo = FirstOrder(X_fede, y_fede, N, d, num_sample, logistic=True, lam=lam, dist=dist)
-    fo_own = FirstOrder(X_fede, y_fede, N, d, num_sample, logistic=True, lam=lam) \
-        if dist is not None else None
+    fo_own = None
     Hmax = np.asarray(Hmax, dtype=np.float64).reshape(-1)[:N]
     alpha = 1.0 / (0.25 * fo.lambda_max() + lam)               # :24
     gd = fo.run_shared(nv.FO_GD, alpha, 0.0, Hmax, T, 0.0, None)
@@ -76,16 +75,18 @@ def gd_dgd_lag_logistic(X, y, num_workers, num_feature, Hmax, num_iter, X_fede, 
 
 
 def dual_averaging(XX, YY, no_workers, num_feature, noSamples, num_iter, obj0, acc, alpha,
-                   mode="faithful", return_state=False):
-    fo = FirstOrder(XX, YY, no_workers, num_feature, noSamples, logistic=False)
+                   mode="faithful", return_state=False, dist=None):
+    fo = FirstOrder(XX, YY, no_workers, num_feature, noSamples, logistic=False,
+                    dist=_dist_or_none(dist))
     obj, loss, it, tv, Theta = fo.run_dualavg(alpha, int(num_iter), obj0, acc, jacobi=(mode == "jacobi"))
     res = (obj, loss, it, tv)
     return res + ({"theta": Theta, "iteration": it},) if return_state else res
 
 
 def dual_averaging_logistic(XX, YY, no_workers, num_feature, noSamples, num_iter, obj0, acc, alpha,
-                            eta, mode="faithful", naive=True, return_state=False):
-    fo = FirstOrder(XX, YY, no_workers, num_feature, noSamples, logistic=True, lam=eta)
+                            eta, mode="faithful", naive=True, return_state=False, dist=None):
+    fo = FirstOrder(XX, YY, no_workers, num_feature, noSamples, logistic=True, lam=eta,
+                    dist=_dist_or_none(dist))
     obj, loss, it, tv, Theta = fo.run_dualavg(alpha, int(num_iter), obj0, acc, jacobi=(mode == "jacobi"))
     res = (obj, loss, it, tv)
     return res + ({"theta": Theta, "iteration": it},) if return_state else res

@@ -55,7 +55,22 @@ class FirstOrder:
         else:
             self.wbuf = torch.empty((N, s), dtype=torch.float64, device=self.dev)
         del G
-        self.Y = torch.zeros((N, self.dp), dtype=torch.float64, device=self.dev)
+        self._own_sym = None
+        if self.dist is not None:
+            # chain-halo tables (DGD / dual averaging across GPUs): Ytab | Ztab[2] | rowflag[2] |
+            # fx[2][W] | fxflag[2][W], indexed by GLOBAL worker id, in symmetric memory
+            NG, dp, W = self.Nglob, self.dp, self.dist.world
+            o_z = NG * dp * 8
+            o_rf = o_z + 2 * NG * dp * 8
+            o_fx = o_rf + (2 * NG * 8 + 255) // 256 * 256
+            o_ff = o_fx + 256 * ((2 * W * 8 + 255) // 256)
+            tot = o_ff + 256 * ((2 * W * 8 + 255) // 256)
+            sym = self.dist.symm_bytes(tot)
+            self._own_sym = (sym, o_z, o_rf, o_fx, o_ff)
+            Ytab = sym.local[:o_z].view(torch.float64).view(NG, dp)
+            self.Y = Ytab[self.gid0:self.gid0 + N]
+        else:
+            self.Y = torch.zeros((N, self.dp), dtype=torch.float64, device=self.dev)
         self.fw = torch.zeros((N,), dtype=torch.float64, device=self.dev)
         self.launches = 0
 
@@ -64,7 +79,7 @@ class FirstOrder:
         """Least-squares engine from device-resident pieces (packed Grams ``P`` (N, packed), ``b``
         (N, dp), ``0.5 y'y`` (N,), ``sum_n G_n`` (dp, dp)): the scaled configs never hold X."""
         self = cls.__new__(cls)
-        self.dist, self.Nglob, self.gid0 = None, int(N), 0
+        self.dist, self.Nglob, self.gid0, self._own_sym = None, int(N), 0, None
         self.dev = device or P.device
         self.N, self.d, self.s, self.logistic, self.lam = int(N), int(d), 0, False, 0.0
         self.dp = nv.padded(self.d)
@@ -252,6 +267,31 @@ class FirstOrder:
         p.ctrl, p.counters = ctrl.data_ptr(), cnt.data_ptr()
         p.step, p.obj0, p.acc = float(step), float(obj0), float(acc)
         p.N, p.d, p.dp, p.max_iter, p.jacobi = N, self.d, dp, T, int(jacobi)
+        p.Nglob, p.gid0, p.rank, p.nranks = self.Nglob, self.gid0, 0, 1
+        p.Ytab = self.Y.data_ptr()
+        keep = []
+        if self._own_sym is not None:
+            sym, o_z, o_rf, o_fx, o_ff = self._own_sym
+            W = self.dist.world
+            torch.cuda.synchronize(dev)
+            self.dist.barrier()                     # nobody is still writing into anybody's tables
+            sym.local[o_z:].zero_()                 # Z halos, row flags, objective ring: versions restart
+            torch.cuda.synchronize(dev)
+            self.dist.barrier()
+            base = sym.local.data_ptr()
+            ftot = torch.zeros((2,), dtype=f64, device=dev)
+
+            def tab(off):
+                return torch.tensor([q + off for q in sym.peer_ptrs], dtype=torch.int64, device=dev)
+
+            yp, zp, rp, fp, ffp = tab(0), tab(o_z), tab(o_rf), tab(o_fx), tab(o_ff)
+            p.Ytab, p.Ztab, p.rowflag = base, base + o_z, base + o_rf
+            p.fx, p.fxflag, p.ftot = base + o_fx, base + o_ff, ftot.data_ptr()
+            p.Ytab_peer, p.Ztab_peer, p.rowflag_peer = yp.data_ptr(), zp.data_ptr(), rp.data_ptr()
+            p.fx_peer, p.fxflag_peer = fp.data_ptr(), ffp.data_ptr()
+            p.rank, p.nranks = self.dist.rank, W
+            keep = [ftot, yp, zp, rp, fp, ffp]
+        self._own_keep = keep
         return p, Theta, Z, obj_h, loss_h, t_h, ctrl, cnt
 
     def run_dgd(self, step, T, obj0, window=256):
@@ -260,10 +300,13 @@ class FirstOrder:
 
         def body():
             self.provider(Theta, self.dp)
+            nv.check(L.gadmm_own_exchange(C.byref(p), 1, nv.stream_ptr()))
             nv.check(L.gadmm_dgd_update(C.byref(p), nv.stream_ptr()))
-            self.launches += 1
+            self.launches += 2 if p.nranks > 1 else 1
 
         self._drive(body, ctrl, T, False, window)
+        if self.dist is not None:
+            self.dist.barrier()
         return obj_h[1:T + 1].cpu().numpy(), loss_h[1:T + 1].cpu().numpy(), self._time(t_h, T)
 
     def run_dualavg(self, alpha, T, obj0, acc, jacobi=False, window=256):
@@ -272,16 +315,25 @@ class FirstOrder:
 
         def body():
             self.provider(Theta, self.dp)
+            nv.check(L.gadmm_own_exchange(C.byref(p), 0, nv.stream_ptr()))
             nv.check(L.gadmm_dualavg_update(C.byref(p), 1, nv.stream_ptr()))
-            self.launches += 1
+            self.launches += 2 if p.nranks > 1 else 1
 
         self._drive(body, ctrl, T, True, window)
         if not int(ctrl[1].item()):
             # close the last iteration: objective of the final iterate
             self.provider(Theta, self.dp)
+            nv.check(L.gadmm_own_exchange(C.byref(p), 0, nv.stream_ptr()))
             nv.check(L.gadmm_dualavg_update(C.byref(p), 0, nv.stream_ptr()))
             torch.cuda.synchronize(self.dev)
         hit = int(ctrl[1].item())
         n = hit if hit else T
+        th = Theta[:, :self.d]
+        if self.dist is not None:               # assemble the full d x N iterate on every rank
+            full = torch.zeros((self.Nglob, self.d), dtype=torch.float64, device=self.dev)
+            full[self.gid0:self.gid0 + self.N] = th
+            self.dist.all_reduce_sum_(full)
+            self.dist.barrier()
+            th = full
         return (obj_h[1:n + 1].cpu().numpy(), loss_h[1:n + 1].cpu().numpy(), n, self._time(t_h, n),
-                Theta[:, :self.d].cpu().numpy().T)
+                th.cpu().numpy().T)

@@ -118,8 +118,13 @@ class GadmmOwn(C.Structure):
     _fields_ = [
         ("Theta", _vp), ("Y", _vp), ("fw", _vp), ("Z", _vp), ("obj_hist", _vp), ("loss_hist", _vp),
         ("t_hist", _vp), ("ctrl", _vp), ("counters", _vp),
+        ("Ytab", _vp), ("Ztab", _vp), ("rowflag", _vp), ("Ytab_peer", _vp), ("Ztab_peer", _vp),
+        ("rowflag_peer", _vp), ("fx", _vp), ("fxflag", _vp), ("fx_peer", _vp), ("fxflag_peer", _vp),
+        ("ftot", _vp),
         ("step", C.c_double), ("obj0", C.c_double), ("acc", C.c_double),
         ("N", C.c_int), ("d", C.c_int), ("dp", C.c_int), ("max_iter", C.c_int), ("jacobi", C.c_int),
+        ("Nglob", C.c_int), ("gid0", C.c_int), ("rank", C.c_int), ("nranks", C.c_int),
+        ("reserved", C.c_int),
     ]
 
 

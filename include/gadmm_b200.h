@@ -221,9 +221,28 @@ typedef struct GadmmOwn {         /* one iterate per worker: DGD, dual averaging
   unsigned long long* t_hist;
   unsigned long long* ctrl;       /* [0]=iteration, [1]=hit, [2]=stop enabled */
   unsigned int* counters;         /* [1] */
+  /* multi-GPU (nranks > 1): workers gid0..gid0+N-1 of Nglob live here (contiguous ranges).  The
+   * tables below are symmetric allocations indexed by GLOBAL worker id; a GPU writes its own rows
+   * locally and pushes its first / last row into the neighbouring GPU's table (NVLink P2P stores
+   * + st.release.sys row flags) -- the chain halo of SURVEY.md K8. */
+  double* Ytab;                   /* [Nglob][dp] gradients; Y == Ytab + gid0*dp */
+  double* Ztab;                   /* [2][Nglob][dp] halo copies of Z, slot = version & 1 */
+  unsigned long long* rowflag;    /* [2][Nglob]: version of the Y / Z halo row present here */
+  double* const* Ytab_peer;       /* [nranks] */
+  double* const* Ztab_peer;
+  unsigned long long* const* rowflag_peer;
+  double* fx;                     /* [2][nranks] objective partials (ring over iterations) */
+  unsigned long long* fxflag;     /* [2][nranks] */
+  double* const* fx_peer;
+  unsigned long long* const* fxflag_peer;
+  double* ftot;                   /* [2] device scalars: all-rank objective of iteration it */
   double step, obj0, acc;
   int N, d, dp, max_iter, jacobi;
+  int Nglob, gid0, rank, nranks, reserved;
 } GadmmOwn;
+/* Objective exchange (+ push of the boundary gradient rows when push_y != 0); a no-op for
+ * nranks == 1.  Launch after the gradient provider, before the update kernel. */
+int gadmm_own_exchange(const GadmmOwn* p, int push_y, void* stream);
 int gadmm_dgd_update(const GadmmOwn* p, void* stream);
 /* update=1: record the objective of the previous iterate (from fw), stop test, then one dual
  * averaging sweep; update=0: record only (closes the last iteration). */

@@ -76,6 +76,14 @@ def main():
         np.testing.assert_allclose(ra[kk], rb[kk], rtol=1e-7, atol=1e-9, err_msg=f"baseline curve {kk}")
     live = int(np.nonzero(ra[7] < 1e-7)[0][0]) if np.any(ra[7] < 1e-7) else 400
     np.testing.assert_array_equal(ra[9][:live], rb[9][:live])
+    # dual averaging along the chain with Z halos over NVLink (Gauss-Seidel order and Jacobi)
+    for mode in ("faithful", "jacobi"):
+        da = O.dual_averaging(Xb, Yb, Nb, db, sb, 300, ob, 1e-4, ra[18], mode=mode, return_state=True)
+        dbb = g.dual_averaging(Xb, Yb, Nb, db, sb, 300, ob, 1e-4, ra[18], mode=mode, backend="b200",
+                               dist=D, return_state=True)
+        assert da[2] == dbb[2], (mode, da[2], dbb[2])
+        np.testing.assert_allclose(da[0], dbb[0], rtol=1e-9, err_msg=f"dual averaging {mode}")
+        np.testing.assert_allclose(da[4]["theta"], dbb[4]["theta"], rtol=1e-8, atol=1e-12)
     D.barrier()
     if D.rank == 0:
         print(f"STAR_NVLS_USED={used}")
