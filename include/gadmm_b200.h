@@ -310,6 +310,19 @@ typedef struct GadmmLogistic {
 int gadmm_logistic_half_gd(const GadmmLogistic* p, int color, void* stream);
 int gadmm_logistic_dual_obj(const GadmmLogistic* p, void* stream);
 
+/* Hessian-free logistic building block for shards too wide for an explicit Hessian (s < d, d up to
+ * 8192): v[n] = X_n' w(X_n x_n) in ONE pass over the fp32 shard X: [N][s][d].
+ *   hv = 0: w = -y ./ (1 + exp(y .* Xx)); also writes Dw = sigma(1-sigma) [N][s] and loss[n] =
+ *           sum log(1 + exp(-y .* Xx))   (data part of the gradient, group_ADMM_logistic.m:48-55)
+ *   hv = 1: w = Dw .* (X x)              (v = X' D X x, the Hessian product of Newton-CG)
+ * x has row stride x_stride doubles (0 = one vector shared by all shards), v row stride ldv.
+ * Shard n of the call is shard n*shard_stride of X / y / Dw (2 = one colour of a chain).
+ * G = CTAs per shard; scratch = gadmm_logistic_xtwx_scratch_elems(N, d, G) doubles. */
+size_t gadmm_logistic_xtwx_scratch_elems(int N, int d, int G);
+int gadmm_logistic_xtwx(const float* X, const double* y, const double* x, long long x_stride,
+                        double* Dw, double* v, int ldv, double* loss, int N, int s, int d, int G,
+                        int hv, int shard_stride, double* scratch, void* stream);
+
 /* ---- tensor-core Gram (K1 proper): G[n] (+)= X_n' diag(w_n) X_n with tcgen05 kind::tf32 in a
  * 3-product hi/lo split (fp32-grade), TMA-fed, TMEM accumulators, fp64 result.  X: [N][s][d] fp64
  * or fp32; w: optional [N][s] row weights (logistic Hessian X'DX); work: gadmm_gram_tc_workspace_floats
