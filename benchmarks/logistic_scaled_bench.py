@@ -1,7 +1,7 @@
 """BASELINE.json config 3 (logistic GADMM, local Newton solves, 512 workers x d = 8192) and the
 throughput of its building block.  Under torchrun the chain is split over the GPUs.
 
-    python benchmarks/logistic_scaled_bench.py --workers 512 --d 8192 --s 1024 --iters 20
+    python benchmarks/logistic_scaled_bench.py --workers 512 --dim 8192 --samples 1024 --iters 20
 """
 import argparse
 import json
@@ -15,8 +15,8 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--workers", type=int, default=512)
-    ap.add_argument("--d", type=int, default=8192)
-    ap.add_argument("--s", type=int, default=1024)
+    ap.add_argument("--dim", dest="d", type=int, default=8192)
+    ap.add_argument("--samples", dest="s", type=int, default=1024)
     ap.add_argument("--rho", type=float, default=0.05)
     ap.add_argument("--lam", type=float, default=1e-3)
     ap.add_argument("--iters", type=int, default=20)

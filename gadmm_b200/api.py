@@ -125,9 +125,21 @@ def group_ADMM_logistic(XX, YY, rho, no_workers, num_feature, per_samples, num_i
     """Exact local solves (CVX in the reference; Newton here) -- group_ADMM_logistic.m:1."""
     b = _resolve(backend)
     if b == "b200":
+        # solver="dense": explicit Hessians (tcgen05 Gram + Cholesky), right for small square shards;
+        # solver="cg": Hessian-free Newton-CG, for wide shards and for multi-GPU runs (dist=...)
+        solver = kw.pop("solver", "auto")
+        if solver == "auto":
+            many = kw.get("dist") is not None and getattr(kw["dist"], "world", 1) > 1
+            solver = "cg" if many or int(num_feature) >= 2048 else "dense"
+        if solver == "cg":
+            return _engine().gadmm_logistic_cg(XX, YY, rho, no_workers, num_feature, per_samples,
+                                               num_iter, obj0, lambda_logistic, acc, **kw)
+        kw.pop("dist", None)
         return _engine().gadmm_logistic_newton(XX, YY, rho, no_workers, num_feature, per_samples,
                                                num_iter, obj0, lambda_logistic, acc, **kw)
     kw.pop("newton_tol", None)
+    kw.pop("solver", None)
+    kw.pop("dist", None)
     return _oracle.group_ADMM_logistic(XX, YY, rho, no_workers, num_feature, per_samples,
                                        num_iter, obj0, lambda_logistic, acc, **kw)
 

@@ -110,3 +110,13 @@ def gadmm_logistic_newton(*a, **kw):
 def logreg_gd_single(*a, **kw):
     from .logistic import logreg_gd_single as _f
     return _f(*a, **kw)
+
+
+def gadmm_logistic_cg(*a, **kw):
+    from .logistic_scaled import gadmm_logistic_cg as _f
+    return _f(*a, **kw)
+
+
+def gadmm_logistic_scaled(*a, **kw):
+    from .logistic_scaled import gadmm_logistic_scaled as _f
+    return _f(*a, **kw)

@@ -311,3 +311,27 @@ def gadmm_logistic_scaled(N: int, d: int, s: int, rho: float, lam_log: float, nu
         st["obj0"] = obj0
         return res + (st,)
     return res
+
+
+def gadmm_logistic_cg(XX, YY, rho, no_workers, num_feature, per_samples, num_iter, obj0,
+                      lambda_logistic, acc, dist: Optional[Dist] = None, newton_tol: float = 1e-9,
+                      faithful: bool = False, fast_hessvec: bool = True, return_state: bool = False,
+                      **_ignored):
+    """``group_ADMM_logistic`` (group_ADMM_logistic.m:1) on host data with the Newton-CG engine:
+    same signature and outputs as the dense-Hessian :func:`gadmm_logistic_newton`, but it scales to
+    wide shards and runs multi-GPU when ``dist`` spans several ranks.  Features are zero-padded to
+    a multiple of 4 (16-byte rows for the bulk copies; a zero column keeps its model entry at 0)."""
+    N, d, s = int(no_workers), int(num_feature), int(per_samples)
+    dpad = (d + 3) // 4 * 4
+    X = np.zeros((N, s, dpad), dtype=np.float32)
+    X[:, :, :d] = np.asarray(XX, dtype=np.float64)[: N * s, :d].reshape(N, s, d)
+    y = np.asarray(YY, dtype=np.float64).reshape(-1)[: N * s].reshape(N, s)
+    eng = ScaledLogisticGadmm(N, dpad, s, lambda_logistic, rho, dist=dist, data=(X, y),
+                              fast_hessvec=fast_hessvec)
+    res = eng.run(num_iter, obj0, acc, newton_tol=newton_tol, faithful=faithful)
+    if return_state:
+        st = eng.state()
+        st["theta"], st["dual"] = st["theta"][:d], st["dual"][:d]
+        st["iteration"] = res[2]
+        return res + (st,)
+    return res

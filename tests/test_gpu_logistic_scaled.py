@@ -82,3 +82,20 @@ def test_scaled_logistic_synthetic_converges():
                                                  acc=1e-4, return_state=True)
     assert it < 200 and loss[-1] < 1e-4
     assert st["hessvecs"] > 0 and st["launches"] > 0
+
+
+def test_api_routes_to_cg_solver():
+    import gadmm_b200 as g
+    rng = np.random.default_rng(9)
+    N, s, d, lam, rho = 5, 20, 10, 1e-3, 5.0            # d % 4 != 0: zero-padded internally
+    XX = rng.standard_normal((N * s, d)).astype(np.float32).astype(np.float64)
+    YY = np.where(rng.standard_normal(N * s) > 0, 1.0, -1.0)
+    obj0 = O.opt_sol_logistic(XX, YY, d, lam, N)
+    args = (XX, YY, rho, N, d, s, 300, obj0, lam, 1e-3)
+    a = O.group_ADMM_logistic(*args, naive=False, return_state=True)
+    b = g.group_ADMM_logistic(*args, backend="b200", solver="cg", return_state=True)
+    c = g.group_ADMM_logistic(*args, backend="b200", solver="dense")
+    assert a[2] == b[2] == c[2] and a[2] < 300
+    np.testing.assert_allclose(a[0], b[0], rtol=1e-8)
+    assert b[4]["theta"].shape == (d, N)
+    np.testing.assert_allclose(a[4]["theta"], b[4]["theta"], rtol=1e-5, atol=1e-7)
