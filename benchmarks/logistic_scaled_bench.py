@@ -21,6 +21,8 @@ def main():
     ap.add_argument("--lam", type=float, default=1e-3)
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--acc", type=float, default=1e-4)
+    ap.add_argument("--rel-acc", type=float, default=0.0, help="stop at gap < rel_acc * obj0 instead of --acc")
+    ap.add_argument("--quiet", action="store_true")
     ap.add_argument("--kernel-only", action="store_true")
     a = ap.parse_args()
     import torch
@@ -57,9 +59,10 @@ def main():
         torch.cuda.synchronize()
         out["optimum_s"] = round(time.time() - t0, 3)
         out["obj0"] = obj0
-        obj, loss, it, tv = eng.run(a.iters, obj0, a.acc, verbose=True)
+        acc = a.rel_acc * abs(obj0) if a.rel_acc > 0 else a.acc
+        obj, loss, it, tv = eng.run(a.iters, obj0, acc, verbose=not a.quiet)
         st = eng.state()
-        out.update({"iterations": int(it), "reached": bool(loss[-1] < a.acc), "final_gap": float(loss[-1]),
+        out.update({"iterations": int(it), "acc": acc, "reached": bool(loss[-1] < acc), "final_gap": float(loss[-1]),
                     "time_s": float(tv[-1]), "s_per_iter": float(tv[-1] / max(len(tv), 1)),
                     "hessvecs": st.get("hessvecs"), "evals": st.get("evals"), "launches": st["launches"]})
     if D.rank == 0:
