@@ -467,8 +467,41 @@ class ChainEngine:
         return num_iter
 
     # ----------------------------------------------------------------------------- results
-    def results(self, Iter: int):
+    def one_worker_solve_seconds(self, reps: int = 21) -> float:
+        """Device time of ONE worker's solve ``theta = M r`` (median of ``reps`` launches of the
+        streaming SYMV on the first local worker's matrix) -- the quantity the reference puts
+        between ``tic`` and ``toc`` (group_ADMM_closedForm.m:40-42,53-55)."""
+        ptrs = self.Mptr[:1].clone()
+        x = torch.ones((1, self.dp), dtype=torch.float64, device=self.dev)
+        y = torch.empty_like(x)
+        scratch = torch.empty((nv.symv_scratch_elems(self.dp),), dtype=torch.float64, device=self.dev)
+        cnt = torch.zeros((1,), dtype=torch.int32, device=self.dev)
+        times = []
+        for k in range(reps + 3):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            nv.check(nv.lib().gadmm_symv_batched(nv.ptr(ptrs), nv.ptr(x), nv.ptr(y), 1, self.dp,
+                                                 self.store, nv.ptr(scratch), nv.ptr(cnt),
+                                                 nv.stream_ptr()))
+            e1.record()
+            e1.synchronize()
+            if k >= 3:
+                times.append(e0.elapsed_time(e1) * 1e-3)
+        return float(np.median(times))
+
+    def results(self, Iter: int, clock: str = "device"):
+        """``(obj, loss, Iter, time)``.  ``clock="device"``: device time since iteration 1, max
+        over ranks.  ``clock="simulated"``: the reference's model of a parallel deployment,
+        ``time(i) = time(i-1) + 2 * (one worker's solve)`` with iteration 1 untimed (SURVEY.md
+        section 5.1); the solve is timed on this GPU."""
         torch.cuda.synchronize(self.dev)
+        if clock == "simulated":
+            obj = self.obj_hist[1:Iter + 1].cpu().numpy().copy()
+            loss = self.loss_hist[1:Iter + 1].cpu().numpy().copy()
+            dt = self.dist.all_reduce_max(self.one_worker_solve_seconds())
+            return obj, loss, Iter, 2.0 * dt * np.arange(Iter, dtype=np.float64)
+        if clock != "device":
+            raise ValueError("clock must be 'device' or 'simulated'")
         obj = self.obj_hist[1:Iter + 1].cpu().numpy().copy()
         loss = self.loss_hist[1:Iter + 1].cpu().numpy().copy()
         t = self.t_hist[1:Iter + 1].to(torch.float64)

@@ -39,7 +39,7 @@ def _energy(cost_of_iter, Iter):
 
 def gadmm_closed_form(XX, YY, rho, no_workers, num_feature, noSamples, num_iter, obj0, acc,
                       store="f64", window=32, dist=None, theta0=None, return_engine=False,
-                      state=None, return_state=False):
+                      state=None, return_state=False, clock="device"):
     """``group_ADMM_closedForm`` on the GPU.  Node-dual form internally; the iterates equal the
     edge-dual ones (nu_n = lambda_n - lambda_{n-1})."""
     eng = _engine(XX, YY, rho, no_workers, num_feature, noSamples, num_iter, obj0, acc, False,
@@ -48,7 +48,7 @@ def gadmm_closed_form(XX, YY, rho, no_workers, num_feature, noSamples, num_iter,
     if state is not None:
         eng.load_state(state)
     it = eng.run(num_iter, window=window)
-    res = eng.results(it)
+    res = eng.results(it, clock=clock)
     if return_state:
         res = res + (eng.state(),)
     return res + (eng,) if return_engine else res

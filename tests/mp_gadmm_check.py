@@ -105,6 +105,20 @@ def main():
     sb = gadmm_logistic_scaled(8, 256, 64, 0.5, 1e-3, 12, 0.0, dist=SoloDist(), return_state=True)
     assert abs(sa[4]["obj0"] - sb[4]["obj0"]) <= 1e-9 * abs(sb[4]["obj0"])
     np.testing.assert_allclose(sa[0], sb[0], rtol=1e-8)
+    # optional protocol stress: GADMM_STRESS_ITERS iterations, a new random
+    # chain every iteration (drawn and switched on the device), split run == single-GPU run
+    stress = int(os.environ.get("GADMM_STRESS_ITERS", "0"))
+    if stress:
+        p0 = np.arange(1, N + 1)
+        sargs = (XX, YY, 1.5, N, d, s, stress, obj0, 0.0, p0, np.ones(N - 1), 1)
+        sm = g.dynamic_group_ADMM_closedForm(*sargs, backend="b200", dist=D, chain_gen="device", rng=5)
+        ss = g.dynamic_group_ADMM_closedForm(*sargs, backend="b200", dist=SoloDist(),
+                                             chain_gen="device", rng=5)
+        assert sm[2] == ss[2] == stress
+        np.testing.assert_allclose(sm[0], ss[0], rtol=1e-9, atol=1e-9)
+        if D.rank == 0:
+            print(f"STRESS_OK iters={stress} final_gap={sm[1][-1]:.3e} "
+                  f"us_per_iter={1e6 * sm[3][-1] / stress:.1f}")
     D.barrier()
     if D.rank == 0:
         print(f"STAR_NVLS_USED={used}")

@@ -140,3 +140,19 @@ def test_dgadmm_with_device_generated_chains(small_linear):
     assert a[2] == b[2]
     np.testing.assert_allclose(a[0], b[0], rtol=1e-9, atol=1e-9)
     np.testing.assert_allclose(a[4], b[4], rtol=1e-12)
+
+
+def test_simulated_clock_mode(small_linear):
+    """clock="simulated": the reference's 2 x (one worker's solve) model, iteration 1 untimed."""
+    p = small_linear
+    obj0 = O.opt_sol_closedForm(p["XX"], p["YY"])
+    args = (p["XX"], p["YY"], 2.0, p["N"], p["d"], p["s"], 3000, obj0, 1e-4)
+    a = g.group_ADMM_closedForm(*args, backend="b200")
+    b = g.group_ADMM_closedForm(*args, backend="b200", clock="simulated")
+    assert a[2] == b[2]
+    np.testing.assert_array_equal(a[0], b[0])
+    t = b[3]
+    assert t.shape == (b[2],) and t[0] == 0.0
+    step = np.diff(t)
+    assert step[0] > 0 and np.allclose(step, step[0], rtol=1e-12)
+    assert 1e-6 < step[0] < 1e-2            # two SYMV launches of a 64x64 problem: microseconds
