@@ -21,6 +21,7 @@
 #include "common.cuh"
 
 #include <cuda.h>
+#include <cstdlib>
 
 namespace gadmm {
 
@@ -246,6 +247,196 @@ gram_tcgen05_kernel(const __grid_constant__ CUtensorMap map_hi,
   }
 }
 
+// ------------------------------------------------------------------------------ CTA-pair variant
+// The single-CTA kernel above moves 64 KiB of operands per 12 MMAs (768 tensor cycles): 85 B/clk
+// per SM, twice what L2 delivers to all 148 SMs at once, and measures at ~51 % tensor activity.
+// Here two CTAs of a cluster (one TPC) share one 256x256 output tile with cta_group::2 MMAs
+// (M = 256: 128 accumulator rows per CTA, N = 256): each CTA loads only its 128 rows of A and its
+// 128-row half of B, so the same 64 KiB per stage now feed 12 MMAs of twice the size.
+//   both CTAs   warp 0 lane 0: TMA (cta_group::2 form, completes on the LEADER's full barrier)
+//   leader      warp 1 lane 0: MMAs for the pair; commits multicast to both CTAs' empty barriers
+//   both CTAs   warps 2-5: epilogue of their own 128 x 256 accumulator half
+// On diagonal tiles a CTA's B half is its own A tile (descriptor aliases it, 2 loads per stage).
+constexpr int GT2 = 256;
+constexpr uint32_t kIdescTf32Pair = (1u << 4) | (2u << 7) | (2u << 10) |
+                                    ((uint32_t)(GT2 >> 3) << 17) | ((uint32_t)(GT2 >> 4) << 24);
+
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::
+                   : "memory");
+}
+__device__ __forceinline__ uint32_t mapa_cta(uint32_t smem_addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(smem_addr), "r"(rank));
+  return r;
+}
+// TMA tile load of the executing CTA's smem, byte count reported to `bar_cluster_addr` (an
+// mbarrier anywhere in the CTA pair)
+__device__ __forceinline__ void tma_load_3d_pair(void* dst, const CUtensorMap* map,
+                                                 uint32_t bar_cluster_addr, int c0, int c1, int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4, %5}], [%2];" ::"r"(smem_u32(dst)),
+      "l"(reinterpret_cast<uint64_t>(map)), "r"(bar_cluster_addr), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
+__device__ __forceinline__ void tc_commit_pair(uint64_t* bar) {   // arrives in both CTAs
+  asm volatile(
+      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64"
+      " [%0], %1;" ::"r"(smem_u32(bar)),
+      "h"((uint16_t)3)
+      : "memory");
+}
+__device__ __forceinline__ void tc_mma_tf32_pair(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc,
+                                                 uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+
+// grid: (2 * lower-triangular 256-tiles, k-segments, N), clusters of 2 along x
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GTHREADS, 1)
+gram_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap map_hi,
+                         const __grid_constant__ CUtensorMap map_lo, int sP, int kseg, int dp,
+                         double* __restrict__ G) {
+  extern __shared__ unsigned char gsm_raw[];
+  unsigned char* base =
+      reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(gsm_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full = reinterpret_cast<uint64_t*>(base + GSTAGES * GSTAGE_BYTES);
+  uint64_t* empty = full + GSTAGES;
+  uint64_t* acc_full = empty + GSTAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_full + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  int I = 0, rem = blockIdx.x >> 1;
+  while (rem > I) { rem -= I + 1; ++I; }
+  const int J = rem, n = blockIdx.z;
+  const bool diag = (I == J);
+  const int k_begin = blockIdx.y * kseg;
+  const int k_end = min(sP, k_begin + kseg);
+  const int nchunks = (k_end - k_begin) / GBK;
+  // The tensor core's fp32 accumulation error grows with the chain length, the epilogue cost
+  // shrinks with it: the first half of the segment accumulates into TMEM columns [0,256), the
+  // second half into [256,512), and the epilogue adds the two in fp64.
+  const int nhalf = (nchunks + 1) / 2;
+  const int arow = I * GT2 + (int)rank * GT;      // this CTA's 128 rows of A (= its accumulator rows)
+  const int brow = J * GT2 + (int)rank * GT;      // this CTA's half of the 256 B rows (tile columns)
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < GSTAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+    mbar_init(acc_full, 1);
+    mbar_fence_init();
+  }
+  if (warp == 1) {   // two 256-column fp32 accumulators in each CTA of the pair (all of TMEM)
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                     smem_u32(tmem_slot)),
+                 "r"(2 * GT2)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();          // the peer's barriers are initialised before anything targets them
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      const uint32_t per_cta = diag ? 2 * GTILE_BYTES : 4 * GTILE_BYTES;
+      for (int c = 0; c < nchunks; ++c) {
+        mbar_wait(&empty[stage], phase ^ 1);
+        unsigned char* st = base + stage * GSTAGE_BYTES;
+        const int k0 = k_begin + c * GBK;
+        if (rank == 0) mbar_arrive_expect_tx(&full[stage], 2 * per_cta);     // both CTAs' bytes
+        const uint32_t lbar = mapa_cta(smem_u32(&full[stage]), 0);
+        tma_load_3d_pair(st, &map_hi, lbar, k0, arow, n);
+        tma_load_3d_pair(st + GTILE_BYTES, &map_lo, lbar, k0, arow, n);
+        if (!diag) {
+          tma_load_3d_pair(st + 2 * GTILE_BYTES, &map_hi, lbar, k0, brow, n);
+          tma_load_3d_pair(st + 3 * GTILE_BYTES, &map_lo, lbar, k0, brow, n);
+        }
+        if (++stage == GSTAGES) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0 && rank == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int c = 0; c < nchunks; ++c) {
+        mbar_wait(&full[stage], phase);
+        tc_fence_after();
+        unsigned char* st = base + stage * GSTAGE_BYTES;
+        const uint64_t a_hi = umma_desc_sw128(st), a_lo = umma_desc_sw128(st + GTILE_BYTES);
+        const uint64_t b_hi = diag ? a_hi : umma_desc_sw128(st + 2 * GTILE_BYTES);
+        const uint64_t b_lo = diag ? a_lo : umma_desc_sw128(st + 3 * GTILE_BYTES);
+#pragma unroll
+        for (int k = 0; k < GBK / 8; ++k) {
+          const uint64_t adv = (uint64_t)((k * 32) >> 4);
+          const uint32_t acc = tmem + (c >= nhalf ? GT2 : 0);
+          tc_mma_tf32_pair(acc, a_hi + adv, b_hi + adv, kIdescTf32Pair,
+                           (k != 0 || (c != 0 && c != nhalf)) ? 1u : 0u);
+          tc_mma_tf32_pair(acc, a_hi + adv, b_lo + adv, kIdescTf32Pair, 1u);
+          tc_mma_tf32_pair(acc, a_lo + adv, b_hi + adv, kIdescTf32Pair, 1u);
+        }
+        tc_commit_pair(&empty[stage]);
+        if (++stage == GSTAGES) { stage = 0; phase ^= 1; }
+      }
+      tc_commit_pair(acc_full);
+    }
+  } else {
+    const int q = warp & 3;
+    mbar_wait(acc_full, 0);
+    tc_fence_after();
+    const int m = q * 32 + lane;
+    double* Gn = G + (size_t)n * dp * dp;
+    const size_t grow = (size_t)arow + m;
+    if (nchunks > 0) {
+      for (int cb = 0; cb < GT2; cb += 32) {
+        if ((size_t)J * GT2 + cb >= (size_t)dp) break;                     // warp-uniform
+        if (diag && (size_t)J * GT2 + cb > (size_t)arow + GT - 1) break;   // above the diagonal
+        uint32_t v[32], v2[32];
+        tmem_ld_32x32b_x32(tmem + ((uint32_t)(q * 32) << 16) + cb, v);
+        if (nchunks > nhalf) {
+          tmem_ld_32x32b_x32(tmem + ((uint32_t)(q * 32) << 16) + GT2 + cb, v2);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v2[j] = 0u;
+        }
+        if (grow < (size_t)dp) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const size_t gcol = (size_t)J * GT2 + cb + j;
+            if (gcol >= (size_t)dp) continue;
+            if (diag && gcol > grow) continue;
+            const double val = (double)__uint_as_float(v[j]) + (double)__uint_as_float(v2[j]);
+            atomicAdd(Gn + grow * dp + gcol, val);
+            if (gcol != grow) atomicAdd(Gn + gcol * dp + grow, val);
+          }
+        }
+      }
+    }
+    tc_fence_before();
+  }
+  __syncthreads();
+  cluster_sync_all();          // nobody leaves (or frees TMEM) while the pair's MMAs may still read
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(2 * GT2)
+                 : "memory");
+  }
+}
+
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
                                   const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
                                   const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
@@ -288,7 +479,10 @@ int gadmm_gram_tcgen05(const void* X, int x_is_f32, const double* w, int N, int 
   GADMM_REQUIRE(N > 0 && s > 0 && d > 0 && dp >= d && dp % 64 == 0, "gram_tcgen05: bad shape");
   cudaStream_t st = (cudaStream_t)stream;
   const int dT = (d + GT - 1) / GT * GT, sP = (s + GBK - 1) / GBK * GBK;
-  if (kseg <= 0) kseg = 2048;
+  // CTA pairs on 256x256 tiles once there are enough of them; GADMM_GRAM_PAIR=0/1 forces a path
+  bool pair = dT >= 512;
+  if (const char* e = getenv("GADMM_GRAM_PAIR")) pair = (e[0] == '1');
+  if (kseg <= 0) kseg = pair ? 4096 : 2048;      // the pair's epilogue is twice as long: amortise it
   kseg = (kseg + GBK - 1) / GBK * GBK;
   float* hi = work;
   float* lo = work + (size_t)N * dT * sP;
@@ -306,11 +500,19 @@ int gadmm_gram_tcgen05(const void* X, int x_is_f32, const double* w, int N, int 
   if (!configured) {
     GADMM_CUDA_OK(cudaFuncSetAttribute(gram_tcgen05_kernel,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, GSMEM));
+    GADMM_CUDA_OK(cudaFuncSetAttribute(gram_tcgen05_pair_kernel,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, GSMEM));
     configured = true;
   }
-  const int nB = dT / GT;
-  dim3 grid(nB * (nB + 1) / 2, (sP + kseg - 1) / kseg, N);
-  gram_tcgen05_kernel<<<grid, GTHREADS, GSMEM, st>>>(mh, ml, sP, kseg, dp, G);
+  if (pair) {
+    const int nB2 = (dT + GT2 - 1) / GT2;
+    dim3 grid(2 * (nB2 * (nB2 + 1) / 2), (sP + kseg - 1) / kseg, N);
+    gram_tcgen05_pair_kernel<<<grid, GTHREADS, GSMEM, st>>>(mh, ml, sP, kseg, dp, G);
+  } else {
+    const int nB = dT / GT;
+    dim3 grid(nB * (nB + 1) / 2, (sP + kseg - 1) / kseg, N);
+    gram_tcgen05_kernel<<<grid, GTHREADS, GSMEM, st>>>(mh, ml, sP, kseg, dp, G);
+  }
   GADMM_CUDA_OK(cudaGetLastError());
   return 0;
 }

@@ -6,7 +6,11 @@ pytestmark = pytest.mark.gpu
 
 
 @pytest.mark.parametrize("N,s,d,dtype", [(2, 64, 128, torch.float32), (3, 50, 50, torch.float64),
-                                         (1, 700, 300, torch.float32), (2, 4500, 256, torch.float32)])
+                                         (1, 700, 300, torch.float32), (2, 4500, 256, torch.float32),
+                                         # dT >= 512: CTA-pair kernel (cta_group::2, 256x256 tiles);
+                                         # 600 -> 640 rows = 2.5 tiles (TMA zero-fills the rest)
+                                         (2, 300, 512, torch.float32), (1, 5000, 600, torch.float32),
+                                         (1, 96, 1100, torch.float64)])
 def test_gram_tc_matches_fp64(N, s, d, dtype):
     from gadmm_b200.ops import linalg as LA
     dev = torch.device("cuda", 0)
