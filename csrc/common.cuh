@@ -14,6 +14,19 @@
 
 namespace gadmm {
 
+// cudaFuncSetAttribute applies to the CURRENT device only: launch helpers remember per device what
+// they have configured (a process that drives several GPUs configures each one on first use).
+struct PerDeviceState {
+  static constexpr int kMax = 64;
+  int v[kMax] = {0};
+  int& here() {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    return v[(dev >= 0 && dev < kMax) ? dev : kMax - 1];
+  }
+};
+
+
 extern thread_local char g_last_error[512];
 int set_error(int code, const char* fmt, ...);
 

@@ -498,11 +498,12 @@ static int launch_symv_grad(const void* const* Sptr, const double* x, long long 
                             const double* b, const double* hyy, double* Y, double* fw, int N,
                             int dp, double* scratch, unsigned int* counters, cudaStream_t st) {
   const int smem = (int)sizeof(SymvSmem<T>);
-  static bool configured = false;
+  static PerDeviceState cfg_state;
+  int& configured = cfg_state.here();
   if (!configured) {
     GADMM_CUDA_OK(cudaFuncSetAttribute(symv_grad_kernel<T>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    configured = true;
+    configured = 1;
   }
   const int nT = dp / kT, npairs = (nT + 1) / 2;
   symv_grad_kernel<T><<<N * npairs, kSymvThreads, smem, st>>>(Sptr, x, xs, b, hyy, Y, fw, dp,

@@ -327,12 +327,13 @@ static int launch_half_impl(const GadmmChain* c, int color, cudaStream_t st) {
 
 template <typename T>
 static int launch_half(const GadmmChain* c, int color, cudaStream_t st) {
-  static bool configured = false;
+  static PerDeviceState cfg_state;
+  int& configured = cfg_state.here();
   constexpr int S1 = SymvCfg<T>::STAGES, S2 = 2 * SymvCfg<T>::STAGES;
   if (!configured) {
     if (int e = configure_half<T, S1>()) return e;
     if (int e = configure_half<T, S2>()) return e;
-    configured = true;
+    configured = 1;
   }
   const int nT = c->dp / kT, npairs = (nT + 1) / 2;
   // about half of the local workers are active per phase

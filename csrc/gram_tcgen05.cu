@@ -496,13 +496,14 @@ int gadmm_gram_tcgen05(const void* X, int x_is_f32, const double* w, int N, int 
   CUtensorMap mh, ml;
   if (int e = make_map(&mh, hi, N, dT, sP)) return e;
   if (int e = make_map(&ml, lo, N, dT, sP)) return e;
-  static bool configured = false;
+  static PerDeviceState cfg_state;
+  int& configured = cfg_state.here();
   if (!configured) {
     GADMM_CUDA_OK(cudaFuncSetAttribute(gram_tcgen05_kernel,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, GSMEM));
     GADMM_CUDA_OK(cudaFuncSetAttribute(gram_tcgen05_pair_kernel,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, GSMEM));
-    configured = true;
+    configured = 1;
   }
   if (pair) {
     const int nB2 = (dT + GT2 - 1) / GT2;

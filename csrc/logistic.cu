@@ -107,7 +107,8 @@ int gadmm_logistic_half_gd(const GadmmLogistic* p, int color, void* stream) {
   const int smem = (2 * p->dp + p->s) * (int)sizeof(double);
   GADMM_REQUIRE(smem <= 200 * 1024, "logistic_half_gd: d=%d, s=%d needs %d B of shared memory "
                 "(> 200 KiB); use the Newton path", p->d, p->s, smem);
-  static int configured = 0;
+  static PerDeviceState cfg_state;
+  int& configured = cfg_state.here();
   if (smem > configured) {
     GADMM_CUDA_OK(cudaFuncSetAttribute(logistic_half_gd_kernel,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, smem));

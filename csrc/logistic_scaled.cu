@@ -236,7 +236,8 @@ int gadmm_logistic_xtwx(const float* X, const double* y, const double* x, long l
   const int rb = (size_t)d * 72 <= 200 * 1024 ? 8 : ((size_t)d * 40 <= 200 * 1024 ? 4 : 2);
   const size_t smem = (size_t)2 * rb * d * sizeof(float) + (size_t)(d + rb + rb * 8) * sizeof(double);
   GADMM_REQUIRE(smem <= 220 * 1024, "logistic_xtwx: d=%d needs %zu B of shared memory", d, smem);
-  static bool configured = false;
+  static PerDeviceState cfg_state;
+  int& configured = cfg_state.here();
   if (!configured) {
     const int cap = 220 * 1024;
     const auto attr = cudaFuncAttributeMaxDynamicSharedMemorySize;
@@ -246,7 +247,7 @@ int gadmm_logistic_xtwx(const float* X, const double* y, const double* x, long l
     GADMM_CUDA_OK(cudaFuncSetAttribute(logistic_xtwx_kernel<8, true>, attr, cap));
     GADMM_CUDA_OK(cudaFuncSetAttribute(logistic_xtwx_kernel<4, true>, attr, cap));
     GADMM_CUDA_OK(cudaFuncSetAttribute(logistic_xtwx_kernel<2, true>, attr, cap));
-    configured = true;
+    configured = 1;
   }
   cudaStream_t st = (cudaStream_t)stream;
   double* part = scratch;

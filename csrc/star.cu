@@ -202,13 +202,14 @@ star_server_kernel(const GadmmStar p) {
 template <typename T>
 static int star_iterate(const GadmmStar* p, int n_iter, cudaStream_t st) {
   const int smem = (int)sizeof(SymvSmem<T>);
-  static bool configured = false;
+  static PerDeviceState cfg_state;
+  int& configured = cfg_state.here();
   if (!configured) {
     GADMM_CUDA_OK(cudaFuncSetAttribute(star_workers_kernel<T>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     GADMM_CUDA_OK(cudaFuncSetAttribute(star_server_kernel<T>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    configured = true;
+    configured = 1;
   }
   const int nT = p->dp / kT, npairs = (nT + 1) / 2;
   for (int i = 0; i < n_iter; ++i) {

@@ -204,7 +204,8 @@ int gadmm_find_path(const double* xy, int N, int model, int* path, double* cost,
   GADMM_REQUIRE(N >= 1 && N <= 8192, "find_path: N=%d out of range [1, 8192]", N);
   GADMM_REQUIRE(model == 0 || model == 1, "find_path: model must be 0 (findPath) or 1 (findPath2)");
   const int smem = N * (2 * (int)sizeof(double) + 1) + 16;
-  static int configured = 0;
+  static PerDeviceState cfg_state;
+  int& configured = cfg_state.here();
   if (smem > 48 * 1024 && smem > configured) {
     GADMM_CUDA_OK(cudaFuncSetAttribute(find_path_kernel,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
