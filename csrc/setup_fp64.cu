@@ -1,8 +1,8 @@
-// One-off setup in fp64 SIMT (K1 exact path, K2, pack):
+// One-off setup in fp64 (K1 exact path, K2, pack); block products on the fp64 tensor path (DMMA):
 //   Gram  G_n = X_n' X_n, b_n = X_n' y_n, 0.5 y_n' y_n        (group_ADMM_closedForm.m:43-45 `H'*H`)
 //   A_n   = G_n + c rho I                                     (same lines, the `\` operand)
 //   A_n^-1 by blocked Cholesky (64-wide panels): potrf + explicit inverse of the diagonal block,
-//          panel = A_ik Linv_kk', trailing SYRK, then W = L^-1 by block forward substitution and
+//          left-looking column update, panel = A_ik Linv_kk', then W = L^-1 by block forward substitution and
 //          A^-1 = W'W.  Everything except the 64x64 diagonal work is a 64x64x64 block product.
 //   pack  lower block-triangle -> 64x64 tiles (fp64 / fp32) for the streaming SYMV.
 // The reference rebuilds and refactors H'H + c rho I in every iteration of every worker; here it
@@ -13,53 +13,83 @@
 namespace gadmm {
 
 constexpr int B = 64;         // block edge
-constexpr int LDS = B + 2;    // padded smem leading dimension (doubles)
-constexpr int kBlkSmem = 2 * B * LDS * (int)sizeof(double);        // As + Bs (dynamic)
+constexpr int LDS = B + 4;    // padded smem leading dimension (doubles): 68 = 4 mod 16 makes both
+                              // fragment access patterns below bank-conflict free
+constexpr int kBlkSmem = 2 * B * LDS * (int)sizeof(double);        // Sa + Sb (dynamic)
 constexpr int kDiagSmem = 2 * B * (B + 1) * (int)sizeof(double);   // L + Li  (dynamic)
 
-// acc(4x4 per thread, 256 threads) += As' * Bs  where As[kk][m], Bs[kk][n] (k-major in smem)
-__device__ __forceinline__ void block_mma(const double (*As)[LDS], const double (*Bs)[LDS],
-                                          double acc[4][4], int ty, int tx, int klen = B) {
-#pragma unroll 8
-  for (int kk = 0; kk < klen; ++kk) {
-    double a[4], b[4];
+// 64x64 block product on the fp64 tensor path: D(8x8) += A(8x4) B(4x8) per warp instruction
+// (mma.sync m8n8k4 f64 -- tcgen05 has no fp64 kind, this is the only tensor-core route for
+// doubles).  Versus a 4x4-per-thread FMA tile it needs a quarter of the shared-memory reads per
+// multiply-add, which is what bounded the SIMT version.
+// 8 warps: warp w owns rows (w>>1)*16..+16 and columns (w&1)*32..+32 of the block, i.e. 2 x 4
+// m8n8 tiles; thread (gid = lane>>2, tig = lane&3) holds c[mt][nt][e] = C(row, col) with
+//   row = (w>>1)*16 + mt*8 + gid,   col = (w&1)*32 + nt*8 + 2*tig + e.
+struct Acc {
+  double c[2][4][2];
+  __device__ __forceinline__ void zero() {
 #pragma unroll
-    for (int i = 0; i < 4; ++i) a[i] = As[kk][ty * 4 + i];
+    for (int a = 0; a < 2; ++a)
 #pragma unroll
-    for (int j = 0; j < 4; ++j) b[j] = Bs[kk][tx * 4 + j];
+      for (int b = 0; b < 4; ++b) c[a][b][0] = c[a][b][1] = 0.0;
+  }
+};
+
+__device__ __forceinline__ void dmma_m8n8k4(double (&c)[2], double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0, %1}, {%2}, {%3}, {%0, %1};"
+               : "+d"(c[0]), "+d"(c[1])
+               : "d"(a), "d"(b));
+}
+
+// acc += A * B over klen (multiple of 4) with both operands in shared memory as plain copies of
+// their global blocks:  A(m,kk) = A_ROWS_M ? Sa[m][kk] : Sa[kk][m],
+//                        B(kk,n) = B_ROWS_N ? Sb[n][kk] : Sb[kk][n].
+template <bool A_ROWS_M, bool B_ROWS_N>
+__device__ __forceinline__ void block_dmma(const double (*Sa)[LDS], const double (*Sb)[LDS], Acc& acc,
+                                           int klen = B) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int gid = lane >> 2, tig = lane & 3;
+  const int wr = (warp >> 1) * 16, wc = (warp & 1) * 32;
+#pragma unroll 4
+  for (int k0 = 0; k0 < klen; k0 += 4) {
+    double a[2], b[4];
 #pragma unroll
-    for (int i = 0; i < 4; ++i)
+    for (int mt = 0; mt < 2; ++mt)
+      a[mt] = A_ROWS_M ? Sa[wr + mt * 8 + gid][k0 + tig] : Sa[k0 + tig][wr + mt * 8 + gid];
 #pragma unroll
-      for (int j = 0; j < 4; ++j) acc[i][j] = fma(a[i], b[j], acc[i][j]);
+    for (int nt = 0; nt < 4; ++nt)
+      b[nt] = B_ROWS_N ? Sb[wc + nt * 8 + gid][k0 + tig] : Sb[k0 + tig][wc + nt * 8 + gid];
+#pragma unroll
+    for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+      for (int nt = 0; nt < 4; ++nt) dmma_m8n8k4(acc.c[mt][nt], a[mt], b[nt]);
   }
 }
 
-// Load a 64x64 block into smem k-major: dst[kk][m] = src(m, kk).
-//   trans == false: src(m,kk) = p[m*ld + kk]   (row-major block, k contiguous)
-//   trans == true : src(m,kk) = p[kk*ld + m]   (m contiguous)
+// f(row, col, value&) over the thread's 16 accumulator entries (block-local coordinates)
+template <typename F>
+__device__ __forceinline__ void acc_for_each(Acc& acc, F&& f) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int gid = lane >> 2, tig = lane & 3;
+  const int wr = (warp >> 1) * 16, wc = (warp & 1) * 32;
+#pragma unroll
+  for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+    for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+      for (int e = 0; e < 2; ++e) f(wr + mt * 8 + gid, wc + nt * 8 + 2 * tig + e, acc.c[mt][nt][e]);
+}
+
+// Copy a 64x64 global block into shared memory as is: dst[r][c] = p[r*ld + c] (coalesced,
+// conflict-free), optionally scaled.
 __device__ __forceinline__ void load_block(double (*dst)[LDS], const double* __restrict__ p,
-                                           size_t ld, bool trans, double scale = 1.0) {
+                                           size_t ld, double scale = 1.0) {
   const int t = threadIdx.x;
-  if (trans) {
 #pragma unroll
-    for (int i = 0; i < 16; ++i) {
-      const int idx = t + i * 256, kk = idx >> 6, m = idx & 63;
-      dst[kk][m] = scale * p[(size_t)kk * ld + m];
-    }
-  } else {
-#pragma unroll
-    for (int i = 0; i < 16; ++i) {
-      const int idx = t + i * 256, m = idx >> 6, kk = idx & 63;
-      dst[kk][m] = scale * p[(size_t)m * ld + kk];
-    }
+  for (int i = 0; i < 16; ++i) {
+    const int idx = t + i * 256, r = idx >> 6, c = idx & 63;
+    dst[r][c] = scale * p[(size_t)r * ld + c];
   }
-}
-
-__device__ __forceinline__ void zero_acc(double acc[4][4]) {
-#pragma unroll
-  for (int i = 0; i < 4; ++i)
-#pragma unroll
-    for (int j = 0; j < 4; ++j) acc[i][j] = 0.0;
 }
 
 // ------------------------------------------------------------------------------------- Gram
@@ -72,9 +102,9 @@ gram_f64_kernel(const double* __restrict__ X, int s, int d, int dp, double* __re
   while (rem > I) { rem -= I + 1; ++I; }
   const int J = rem;
   const double* Xn = X + (size_t)n * s * d;
-  const int t = threadIdx.x, ty = t >> 4, tx = t & 15;
-  double acc[4][4];
-  zero_acc(acc);
+  const int t = threadIdx.x;
+  Acc acc;
+  acc.zero();
   for (int k0 = 0; k0 < s; k0 += 16) {
     // 16 x 64 slices of X for the I columns and the J columns (coalesced along features)
 #pragma unroll
@@ -85,18 +115,15 @@ gram_f64_kernel(const double* __restrict__ X, int s, int d, int dp, double* __re
       Bs[kk][m] = (row < s && cj < d) ? Xn[(size_t)row * d + cj] : 0.0;
     }
     __syncthreads();
-    block_mma(As, Bs, acc, ty, tx, 16);
+    block_dmma<false, false>(As, Bs, acc, 16);      // G_IJ(m,nn) += X(kk, I m) X(kk, J nn)
     __syncthreads();
   }
   double* Gn = G + (size_t)n * dp * dp;
-#pragma unroll
-  for (int i = 0; i < 4; ++i)
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const int r = I * B + ty * 4 + i, cidx = J * B + tx * 4 + j;
-      Gn[(size_t)r * dp + cidx] = acc[i][j];
-      Gn[(size_t)cidx * dp + r] = acc[i][j];
-    }
+  acc_for_each(acc, [&](int r, int c, double& v) {
+    const int gr = I * B + r, gc = J * B + c;
+    Gn[(size_t)gr * dp + gc] = v;
+    Gn[(size_t)gc * dp + gr] = v;
+  });
 }
 
 // b_n = X_n' y_n (one CTA per (n, 64-feature block)), hyy_n = 0.5 y'y
@@ -174,52 +201,46 @@ potrf_diag_kernel(double* __restrict__ A, double* __restrict__ Dinv, int dp, int
   }
 }
 
-// Panel: L_ik = A_ik * Linv_kk'  for i = k+1..nT-1   (grid: (nT-k-1, N))
+// Left-looking block column j, tiles i >= j:  A_ij -= sum_{k<j} L_ik L_jk'  accumulated in
+// registers over the whole k range (one read-modify-write of A_ij per factorisation instead of one
+// per panel, which made the right-looking version memory bound).  grid: (nT - j, N)
+__global__ void __launch_bounds__(256)
+chol_update_kernel(double* __restrict__ A, int dp, int nT, int j) {
+  extern __shared__ __align__(16) unsigned char dsm[];
+  double (*Sa)[LDS] = reinterpret_cast<double (*)[LDS]>(dsm);
+  double (*Sb)[LDS] = Sa + B;
+  const int n = blockIdx.y, i = j + blockIdx.x;
+  double* An = A + (size_t)n * dp * dp;
+  Acc acc;
+  acc.zero();
+  for (int k = 0; k < j; ++k) {
+    load_block(Sa, An + (size_t)i * B * dp + (size_t)k * B, dp);   // L_ik(m,kk)
+    load_block(Sb, An + (size_t)j * B * dp + (size_t)k * B, dp);   // L_jk(nn,kk)
+    __syncthreads();
+    block_dmma<true, true>(Sa, Sb, acc);
+    __syncthreads();
+  }
+  double* Cij = An + (size_t)i * B * dp + (size_t)j * B;
+  acc_for_each(acc, [&](int r, int c, double& v) { Cij[(size_t)r * dp + c] -= v; });
+}
+
+// Panel: L_ij = A_ij * Linv_jj'  for i = j+1..nT-1   (grid: (nT-j-1, N))
 __global__ void __launch_bounds__(256)
 panel_kernel(double* __restrict__ A, const double* __restrict__ Dinv, int dp, int nT, int k) {
   extern __shared__ __align__(16) unsigned char dsm[];
-  double (*As)[LDS] = reinterpret_cast<double (*)[LDS]>(dsm);
-  double (*Bs)[LDS] = As + B;
+  double (*Sa)[LDS] = reinterpret_cast<double (*)[LDS]>(dsm);
+  double (*Sb)[LDS] = Sa + B;
   const int n = blockIdx.y, i = k + 1 + blockIdx.x;
   double* Aik = A + (size_t)n * dp * dp + (size_t)i * B * dp + (size_t)k * B;
   const double* Dk = Dinv + ((size_t)n * nT + k) * B * B;
   // C(m,nn) = sum_kk A_ik(m,kk) * Linv(nn,kk)
-  load_block(As, Aik, dp, false);
-  load_block(Bs, Dk, B, false);     // Bs[kk][nn] = Linv(nn,kk)
+  load_block(Sa, Aik, dp);
+  load_block(Sb, Dk, B);
   __syncthreads();
-  const int ty = threadIdx.x >> 4, tx = threadIdx.x & 15;
-  double acc[4][4];
-  zero_acc(acc);
-  block_mma(As, Bs, acc, ty, tx);
-#pragma unroll
-  for (int a = 0; a < 4; ++a)
-#pragma unroll
-    for (int b2 = 0; b2 < 4; ++b2) Aik[(size_t)(ty * 4 + a) * dp + tx * 4 + b2] = acc[a][b2];
-}
-
-// Trailing update: A_ij -= L_ik L_jk'   for k < j <= i   (grid: (pairs, N))
-__global__ void __launch_bounds__(256)
-syrk_kernel(double* __restrict__ A, int dp, int nT, int k) {
-  extern __shared__ __align__(16) unsigned char dsm[];
-  double (*As)[LDS] = reinterpret_cast<double (*)[LDS]>(dsm);
-  double (*Bs)[LDS] = As + B;
-  const int n = blockIdx.y;
-  int ii = 0, rem = blockIdx.x;
-  while (rem > ii) { rem -= ii + 1; ++ii; }
-  const int i = k + 1 + ii, j = k + 1 + rem;
-  double* An = A + (size_t)n * dp * dp;
-  load_block(As, An + (size_t)i * B * dp + (size_t)k * B, dp, false);
-  load_block(Bs, An + (size_t)j * B * dp + (size_t)k * B, dp, false);
-  __syncthreads();
-  const int ty = threadIdx.x >> 4, tx = threadIdx.x & 15;
-  double acc[4][4];
-  zero_acc(acc);
-  block_mma(As, Bs, acc, ty, tx);
-  double* Cij = An + (size_t)i * B * dp + (size_t)j * B;
-#pragma unroll
-  for (int a = 0; a < 4; ++a)
-#pragma unroll
-    for (int b2 = 0; b2 < 4; ++b2) Cij[(size_t)(ty * 4 + a) * dp + tx * 4 + b2] -= acc[a][b2];
+  Acc acc;
+  acc.zero();
+  block_dmma<true, true>(Sa, Sb, acc);
+  acc_for_each(acc, [&](int r, int c, double& v) { Aik[(size_t)r * dp + c] = v; });
 }
 
 // Row i of W = L^-1:  W_ik = -Linv_ii * sum_{j=k}^{i-1} L_ij W_jk  (k < i),  W_ii = Linv_ii.
@@ -228,35 +249,28 @@ __global__ void __launch_bounds__(256)
 trtri_row_kernel(const double* __restrict__ L, double* __restrict__ W,
                  const double* __restrict__ Dinv, int dp, int nT, int i) {
   extern __shared__ __align__(16) unsigned char dsm[];
-  double (*As)[LDS] = reinterpret_cast<double (*)[LDS]>(dsm);
-  double (*Bs)[LDS] = As + B;
+  double (*Sa)[LDS] = reinterpret_cast<double (*)[LDS]>(dsm);
+  double (*Sb)[LDS] = Sa + B;
   const int n = blockIdx.y, k = blockIdx.x;
   const double* Ln = L + (size_t)n * dp * dp;
   double* Wn = W + (size_t)n * dp * dp;
-  const int ty = threadIdx.x >> 4, tx = threadIdx.x & 15;
-  double acc[4][4];
-  zero_acc(acc);
+  Acc acc;
+  acc.zero();
   for (int j = k; j < i; ++j) {
-    load_block(As, Ln + (size_t)i * B * dp + (size_t)j * B, dp, false);   // L_ij(m,kk)
-    load_block(Bs, Wn + (size_t)j * B * dp + (size_t)k * B, dp, true);    // W_jk(kk,nn)
+    load_block(Sa, Ln + (size_t)i * B * dp + (size_t)j * B, dp);   // L_ij(m,kk)
+    load_block(Sb, Wn + (size_t)j * B * dp + (size_t)k * B, dp);   // W_jk(kk,nn)
     __syncthreads();
-    block_mma(As, Bs, acc, ty, tx);
+    block_dmma<true, false>(Sa, Sb, acc);
     __syncthreads();
   }
-  // T = acc (64x64) -> smem (k-major: Bs[kk][nn] = T(kk,nn)), then W_ik = -Linv_ii * T
-#pragma unroll
-  for (int a = 0; a < 4; ++a)
-#pragma unroll
-    for (int b2 = 0; b2 < 4; ++b2) Bs[ty * 4 + a][tx * 4 + b2] = acc[a][b2];
-  load_block(As, Dinv + ((size_t)n * nT + i) * B * B, B, false, -1.0);   // As[kk][m] = -Linv(m,kk)
+  // T = acc (64x64) -> Sb[kk][nn], then W_ik = -Linv_ii * T
+  acc_for_each(acc, [&](int r, int c, double& v) { Sb[r][c] = v; });
+  load_block(Sa, Dinv + ((size_t)n * nT + i) * B * B, B, -1.0);    // -Linv_ii(m,kk)
   __syncthreads();
-  zero_acc(acc);
-  block_mma(As, Bs, acc, ty, tx);
+  acc.zero();
+  block_dmma<true, false>(Sa, Sb, acc);
   double* Wik = Wn + (size_t)i * B * dp + (size_t)k * B;
-#pragma unroll
-  for (int a = 0; a < 4; ++a)
-#pragma unroll
-    for (int b2 = 0; b2 < 4; ++b2) Wik[(size_t)(ty * 4 + a) * dp + tx * 4 + b2] = acc[a][b2];
+  acc_for_each(acc, [&](int r, int c, double& v) { Wik[(size_t)r * dp + c] = v; });
 }
 
 // W diagonal blocks = Dinv (grid: (nT, N), 256 threads)
@@ -272,28 +286,24 @@ trtri_diag_kernel(double* __restrict__ W, const double* __restrict__ Dinv, int d
 __global__ void __launch_bounds__(256)
 lauum_kernel(const double* __restrict__ W, double* __restrict__ M, int dp, int nT) {
   extern __shared__ __align__(16) unsigned char dsm[];
-  double (*As)[LDS] = reinterpret_cast<double (*)[LDS]>(dsm);
-  double (*Bs)[LDS] = As + B;
+  double (*Sa)[LDS] = reinterpret_cast<double (*)[LDS]>(dsm);
+  double (*Sb)[LDS] = Sa + B;
   const int n = blockIdx.y;
   int i = 0, rem = blockIdx.x;
   while (rem > i) { rem -= i + 1; ++i; }
   const int j = rem;
   const double* Wn = W + (size_t)n * dp * dp;
-  const int ty = threadIdx.x >> 4, tx = threadIdx.x & 15;
-  double acc[4][4];
-  zero_acc(acc);
+  Acc acc;
+  acc.zero();
   for (int k = i; k < nT; ++k) {
-    load_block(As, Wn + (size_t)k * B * dp + (size_t)i * B, dp, true);   // As[kk][m] = W_ki(kk,m)
-    load_block(Bs, Wn + (size_t)k * B * dp + (size_t)j * B, dp, true);   // Bs[kk][nn] = W_kj(kk,nn)
+    load_block(Sa, Wn + (size_t)k * B * dp + (size_t)i * B, dp);   // W_ki(kk,m)
+    load_block(Sb, Wn + (size_t)k * B * dp + (size_t)j * B, dp);   // W_kj(kk,nn)
     __syncthreads();
-    block_mma(As, Bs, acc, ty, tx);
+    block_dmma<false, false>(Sa, Sb, acc);
     __syncthreads();
   }
   double* Mij = M + (size_t)n * dp * dp + (size_t)i * B * dp + (size_t)j * B;
-#pragma unroll
-  for (int a = 0; a < 4; ++a)
-#pragma unroll
-    for (int b2 = 0; b2 < 4; ++b2) Mij[(size_t)(ty * 4 + a) * dp + tx * 4 + b2] = acc[a][b2];
+  acc_for_each(acc, [&](int r, int c, double& v) { Mij[(size_t)r * dp + c] = v; });
 }
 
 // ------------------------------------------------------------------------------------- pack
@@ -348,16 +358,14 @@ int gadmm_spd_inverse_f64(double* A, double* W, double* Dinv, int N, int dp, voi
   const int nT = dp / B;
   GADMM_CUDA_OK(cudaFuncSetAttribute(potrf_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kDiagSmem));
   GADMM_CUDA_OK(cudaFuncSetAttribute(panel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kBlkSmem));
-  GADMM_CUDA_OK(cudaFuncSetAttribute(syrk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kBlkSmem));
+  GADMM_CUDA_OK(cudaFuncSetAttribute(chol_update_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kBlkSmem));
   GADMM_CUDA_OK(cudaFuncSetAttribute(trtri_row_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kBlkSmem));
   GADMM_CUDA_OK(cudaFuncSetAttribute(lauum_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kBlkSmem));
-  for (int k = 0; k < nT; ++k) {
+  for (int k = 0; k < nT; ++k) {       // left-looking: bring column k up to date, factor, solve
+    if (k > 0) chol_update_kernel<<<dim3(nT - k, N), 256, kBlkSmem, st>>>(A, dp, nT, k);
     potrf_diag_kernel<<<N, 64, kDiagSmem, st>>>(A, Dinv, dp, nT, k);
     const int rest = nT - k - 1;
-    if (rest > 0) {
-      panel_kernel<<<dim3(rest, N), 256, kBlkSmem, st>>>(A, Dinv, dp, nT, k);
-      syrk_kernel<<<dim3(rest * (rest + 1) / 2, N), 256, kBlkSmem, st>>>(A, dp, nT, k);
-    }
+    if (rest > 0) panel_kernel<<<dim3(rest, N), 256, kBlkSmem, st>>>(A, Dinv, dp, nT, k);
   }
   GADMM_CUDA_OK(cudaMemsetAsync(W, 0, (size_t)N * dp * dp * sizeof(double), st));
   trtri_diag_kernel<<<dim3(nT, N), 256, 0, st>>>(W, Dinv, dp, nT);
