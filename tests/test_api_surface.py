@@ -30,6 +30,9 @@ def test_public_names_and_engine_targets():
         # the public wrapper takes the same positional arguments plus backend=
         sig = inspect.signature(getattr(g, name))
         sig.bind(*range(arity), backend="oracle")
+    # the Newton-CG solver behind group_ADMM_logistic(solver="cg") takes the same arguments
+    inspect.signature(engine.gadmm_logistic_cg).bind(*range(10), dist=None, return_state=True)
+    inspect.signature(engine.gadmm_closed_form).bind(*range(9), clock="simulated")
     for name in ("findPath", "findPath2", "calc_cost", "opt_sol", "opt_sol_logistic", "logReg_GD",
                  "group_ADMM", "standard_ADMM"):
         assert callable(getattr(g, name))
@@ -73,3 +76,26 @@ def test_ctypes_mirrors_match_header_sizes():
                 raise AssertionError(f"unparsed member in {name}: {decl!r}")
         size = (size + 7) // 8 * 8
         assert ctypes.sizeof(getattr(nv, name)) == size, (name, ctypes.sizeof(getattr(nv, name)), size)
+
+
+def test_header_declares_every_exported_entry_point():
+    """Every extern "C" function defined in csrc/ is declared in include/gadmm_b200.h, and every
+    native call made from Python names a declared function."""
+    import glob
+    import os
+    import re
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    hdr = open(os.path.join(root, "include", "gadmm_b200.h")).read()
+    declared = set(re.findall(r"\b(gadmm_[a-z0-9_]+)\s*\(", hdr))
+    defined = set()
+    for f in glob.glob(os.path.join(root, "csrc", "*.cu")):
+        src = open(f).read()
+        if 'extern "C"' not in src:
+            continue
+        ext = src[src.index('extern "C"'):]
+        defined |= set(re.findall(r"^(?:int|size_t|const char\*)\s+(gadmm_[a-z0-9_]+)\s*\(", ext, re.M))
+    assert defined and defined <= declared, sorted(defined - declared)
+    called = set()
+    for f in glob.glob(os.path.join(root, "gadmm_b200", "**", "*.py"), recursive=True):
+        called |= set(re.findall(r"(?:lib\(\)|\bL|_lib)\.(gadmm_[a-z0-9_]+)", open(f).read()))
+    assert called <= declared, sorted(called - declared)
