@@ -114,6 +114,26 @@ def logistic(D, a):
          Iter=int(r[2]), wall_s=time.perf_counter() - t0, final_loss=float(r[1][-1]))
 
 
+def logistic_scaled(D, a):
+    """Config 3 at full size: logistic GADMM, exact local solves (Newton-CG), chain split over the
+    GPUs of the job (--ls-workers x --ls-d x --ls-s, default 512 x 8192 x 1024)."""
+    import torch
+    from gadmm_b200.engine.logistic_scaled import ScaledLogisticGadmm
+    t0 = time.time()
+    eng = ScaledLogisticGadmm(a.ls_workers, a.ls_d, a.ls_s, 1e-3, a.ls_rho, dist=D)
+    obj0, _ = eng.solve_optimum()
+    torch.cuda.synchronize()
+    setup = time.time() - t0
+    acc = a.ls_rel_acc * abs(obj0)
+    obj, loss, it, tv = eng.run(a.ls_iters, obj0, acc)
+    st = eng.state()
+    emit(D, config=f"logistic {a.ls_workers} workers x d={a.ls_d} x s={a.ls_s}, rho={a.ls_rho}",
+         algo="GADMM logistic (Newton-CG local solves)", gpus=D.world, setup_s=setup, Iter=int(it),
+         reached=bool(loss[-1] < acc), rel_gap=float(loss[-1] / abs(obj0)), time_s=float(tv[-1]),
+         ms_per_iter=1e3 * float(tv[-1]) / max(len(tv), 1), hessvecs=st.get("hessvecs"),
+         evals=st.get("evals"), launches=st["launches"])
+
+
 def baselines_scaled(D, a):
     """Config 2, the "vs" list at the scaled shape on ONE GPU: iteration rate of every first-order
     baseline (gradient provider = streaming SYMV over all packed Grams + one fused update kernel)."""
@@ -160,6 +180,12 @@ def main():
     ap.add_argument("--lg-workers", type=int, default=16)
     ap.add_argument("--lg-s", type=int, default=512)
     ap.add_argument("--lg-d", type=int, default=256)
+    ap.add_argument("--ls-workers", type=int, default=512)
+    ap.add_argument("--ls-d", type=int, default=8192)
+    ap.add_argument("--ls-s", type=int, default=1024)
+    ap.add_argument("--ls-rho", type=float, default=0.3)
+    ap.add_argument("--ls-iters", type=int, default=30)
+    ap.add_argument("--ls-rel-acc", type=float, default=1e-4)
     a = ap.parse_args()
     import torch
     from gadmm_b200.parallel.runtime import Dist, init_process_group
@@ -169,6 +195,7 @@ def main():
     todo = a.which.split(",")
     for name, fn in (("reference", reference_shape), ("dgadmm", dgadmm),
                      ("t3", one_worker_per_gpu), ("logistic", logistic),
+                     ("logistic_scaled", logistic_scaled),
                      ("baselines", baselines_scaled)):
         if "all" in todo or name in todo:
             fn(D, a)
