@@ -25,11 +25,11 @@ logistic_half_gd_kernel(const GadmmLogistic p, const int color) {
   const unsigned long long it = p.ctrl[0];
   if (p.ctrl[2] != 0ull && p.ctrl[1] != 0ull) return;
   if (it > (unsigned long long)p.max_iter) return;
-  const int n = blockIdx.x;
+  const int n = p.n0 + blockIdx.x;                   // global worker; shards are indexed locally
   if ((n & 1) != color) return;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, d = p.d, s = p.s, dp = p.dp;
-  const double* Xn = p.X + (size_t)n * s * d;
-  const double* yn = p.y + (size_t)n * s;
+  const double* Xn = p.X + (size_t)blockIdx.x * s * d;
+  const double* yn = p.y + (size_t)blockIdx.x * s;
   double* th = p.theta + (size_t)n * dp;
   const bool hasL = n > 0, hasR = n < p.N - 1;
   for (int j = tid; j < d; j += 256) {
@@ -114,7 +114,10 @@ int gadmm_logistic_half_gd(const GadmmLogistic* p, int color, void* stream) {
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     configured = smem;
   }
-  logistic_half_gd_kernel<<<p->N, 256, smem, (cudaStream_t)stream>>>(*p, color);
+  GadmmLogistic q = *p;
+  if (q.nloc <= 0) { q.n0 = 0; q.nloc = q.N; }
+  GADMM_REQUIRE(q.n0 >= 0 && q.n0 + q.nloc <= q.N, "logistic_half_gd: bad worker range");
+  logistic_half_gd_kernel<<<q.nloc, 256, smem, (cudaStream_t)stream>>>(q, color);
   GADMM_CUDA_OK(cudaGetLastError());
   return 0;
 }

@@ -47,8 +47,13 @@ class _LogisticState:
 
 
 def gadmm_logistic_gd(XX, YY, rho, no_workers, num_feature, per_samples, num_iter, obj0,
-                      lambda_logistic, acc, gdStep, naive=True, window=16, return_state=False):
-    """``group_ADMM_logistic_GD`` on the GPU: ``(obj, loss, Iter, time)``."""
+                      lambda_logistic, acc, gdStep, naive=True, window=16, return_state=False,
+                      dist=None):
+    """``group_ADMM_logistic_GD`` on the GPU: ``(obj, loss, Iter, time)``.  With a multi-rank
+    ``dist`` the chain is split over the GPUs (:func:`_gadmm_logistic_gd_dist`)."""
+    if dist is not None and getattr(dist, "world", 1) > 1:
+        return _gadmm_logistic_gd_dist(XX, YY, rho, no_workers, num_feature, per_samples, num_iter,
+                                       obj0, lambda_logistic, acc, gdStep, dist, return_state)
     st = _LogisticState(XX, YY, no_workers, num_feature, per_samples, lambda_logistic)
     dev, T = st.dev, int(num_iter)
     f64 = torch.float64
@@ -100,6 +105,92 @@ def gadmm_logistic_gd(XX, YY, rho, no_workers, num_feature, per_samples, num_ite
     if return_state:
         return res + ({"theta": st.theta[:, :st.d].cpu().numpy().T, "dual": st.lam[:, :st.d].cpu().numpy().T,
                        "iteration": it, "inner_steps": int(inner.item()), "launches": st.launches},)
+    return res
+
+
+def _gadmm_logistic_gd_dist(XX, YY, rho, N, d, s, num_iter, obj0, lam_log, acc, gdStep, dist,
+                            return_state=False):
+    """Inexact-solve logistic GADMM with contiguous chain segments per GPU.  Same kernels as the
+    single-GPU path (``logistic_half_gd_kernel`` on the rank's workers, the fused loss kernel); the
+    model table is a symmetric buffer replicated on every rank, a rank stores its boundary models
+    into the neighbouring rank's replica over NVLink after each colour, and the ranks meet at a
+    barrier (an outer iteration is up to 200 inner gradient steps per worker, so the exchange is
+    not worth fusing).  Duals of the one edge that crosses into a rank are recomputed there."""
+    from ..parallel.runtime import partition
+    dev = dist.device
+    N, d, s, T = int(N), int(d), int(s), int(num_iter)
+    dp = nv.padded(d)
+    owner = partition(N, dist.world)
+    mine = np.nonzero(owner == dist.rank)[0]
+    if mine.size == 0:
+        raise ValueError("more ranks than workers")
+    g0, nloc = int(mine[0]), int(mine.size)
+    f64 = torch.float64
+    XXa = np.asarray(XX, dtype=np.float64)[: N * s, :d].reshape(N, s, d)[g0:g0 + nloc]
+    YYa = np.asarray(YY, dtype=np.float64).reshape(-1)[: N * s].reshape(N, s)[g0:g0 + nloc]
+    X = torch.from_numpy(np.ascontiguousarray(XXa)).to(dev)
+    y = torch.from_numpy(np.ascontiguousarray(YYa)).to(dev)
+    sym = dist.symm_bytes(N * dp * 8)
+    theta = sym.local[: N * dp * 8].view(f64).view(N, dp)
+    lam = torch.zeros((N, dp), dtype=f64, device=dev)
+    fw = torch.zeros((nloc,), dtype=f64, device=dev)
+    Yg = torch.zeros((nloc, dp), dtype=f64, device=dev)
+    wbuf = torch.zeros((nloc, s), dtype=f64, device=dev)
+    ctrl = torch.tensor([1, 0, 0, 0], dtype=torch.int64, device=dev)      # stop decided on the host
+    inner = torch.zeros((1,), dtype=torch.int64, device=dev)
+    p = nv.GadmmLogistic()
+    p.X, p.y, p.theta, p.lam, p.fw = X.data_ptr(), y.data_ptr(), theta.data_ptr(), lam.data_ptr(), fw.data_ptr()
+    p.inner_steps, p.ctrl = inner.data_ptr(), ctrl.data_ptr()
+    p.rho, p.lam_log, p.gd_step, p.inner_tol = float(rho), float(lam_log), float(gdStep), 1e-4
+    p.obj0, p.acc = float(obj0), float(acc)
+    p.N, p.s, p.d, p.dp, p.max_iter, p.max_inner = N, s, d, dp, T + 1, 100
+    p.n0, p.nloc = g0, nloc
+    L = nv.lib()
+
+    def push(colour):
+        for gid, nb in ((g0, g0 - 1), (g0 + nloc - 1, g0 + nloc)):
+            if gid % 2 == colour and 0 <= nb < N:
+                view = sym.handle.get_buffer(int(owner[nb]), (N, dp), f64)
+                view[gid].copy_(theta[gid])
+
+    lo, hi = max(g0 - 1, 0), min(g0 + nloc, N - 1)       # edges lo .. hi-1 touch this rank
+    obj, loss, tv = [], [], []
+    it, hit = T, False
+    dist.barrier()
+    ev0 = torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for i in range(1, T + 1):
+        for colour in (0, 1):
+            nv.check(L.gadmm_logistic_half_gd(C.byref(p), colour, nv.stream_ptr()))
+            push(colour)
+            dist.barrier()
+        lam[lo:hi] += rho * (theta[lo:hi] - theta[lo + 1:hi + 1])
+        nv.check(L.gadmm_logistic_grad(nv.ptr(X), nv.ptr(y), nv.ptr(theta[g0:]), C.c_longlong(dp),
+                                       C.c_double(lam_log), nloc, s, d, dp, nv.ptr(Yg), nv.ptr(fw),
+                                       nv.ptr(None), nv.ptr(wbuf), nv.stream_ptr()))
+        tot = fw.sum().reshape(1)
+        dist.all_reduce_sum_(tot)
+        f = float(tot.item())
+        obj.append(f)
+        loss.append(abs(f - obj0))
+        ev = torch.cuda.Event(enable_timing=True)
+        ev.record()
+        ev.synchronize()
+        tv.append(ev0.elapsed_time(ev) * 1e-3)
+        if loss[-1] < acc:
+            it, hit = i, True
+            break
+    n_out = it if hit else len(obj)
+    tvec = torch.tensor(tv[:n_out], dtype=f64, device=dev)
+    if n_out:
+        tvec = tvec - tvec[0].clone()
+        torch.distributed.all_reduce(tvec, op=torch.distributed.ReduceOp.MAX)
+    res = (np.asarray(obj[:n_out]), np.asarray(loss[:n_out]), it, tvec.cpu().numpy())
+    if return_state:
+        dist.all_reduce_sum_(inner)
+        return res + ({"theta": theta[g0:g0 + nloc, :d].cpu().numpy().T,
+                       "dual": lam[g0:g0 + nloc, :d].cpu().numpy().T, "g0": g0, "iteration": it,
+                       "inner_steps": int(inner.item())},)
     return res
 
 

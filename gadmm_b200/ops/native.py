@@ -155,7 +155,7 @@ class GadmmLogistic(C.Structure):
         ("rho", C.c_double), ("lam_log", C.c_double), ("gd_step", C.c_double),
         ("inner_tol", C.c_double), ("obj0", C.c_double), ("acc", C.c_double),
         ("N", C.c_int), ("s", C.c_int), ("d", C.c_int), ("dp", C.c_int), ("max_iter", C.c_int),
-        ("max_inner", C.c_int),
+        ("max_inner", C.c_int), ("n0", C.c_int), ("nloc", C.c_int),
     ]
 
 

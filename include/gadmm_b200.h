@@ -293,8 +293,8 @@ int gadmm_star_iterate(const GadmmStar* p, int n_iter, void* stream);
 
 /* ---- logistic GADMM, inexact local solves (K9; group_ADMM_logistic_GD.m, logReg_GD.m) ------- */
 typedef struct GadmmLogistic {
-  const double* X;           /* [N][s][d] */
-  const double* y;           /* [N][s]   labels +-1 */
+  const double* X;           /* [nloc][s][d] */
+  const double* y;           /* [nloc][s]   labels +-1 */
   double* theta;             /* [N][dp] */
   double* lam;               /* [N][dp]  edge duals: lam[n] couples workers n and n+1 */
   const double* fw;          /* [N] per-worker objective (from gadmm_logistic_grad) */
@@ -306,6 +306,8 @@ typedef struct GadmmLogistic {
   unsigned long long* t_hist;
   double rho, lam_log, gd_step, inner_tol, obj0, acc;
   int N, s, d, dp, max_iter, max_inner;
+  int n0, nloc;              /* half_gd handles workers n0..n0+nloc-1 (nloc <= 0: all N); X, y, fw hold
+                                only those shards, theta / lam are [N][dp] tables (multi-GPU: replicas) */
 } GadmmLogistic;
 int gadmm_logistic_half_gd(const GadmmLogistic* p, int color, void* stream);
 int gadmm_logistic_dual_obj(const GadmmLogistic* p, void* stream);

@@ -98,6 +98,13 @@ def main():
     g0l = lb[4]["g0"]
     np.testing.assert_allclose(la[4]["theta"][:, g0l:g0l + lb[4]["theta"].shape[1]], lb[4]["theta"],
                                rtol=1e-5, atol=1e-7)
+    # the reference's inexact local solve (<= 100 frozen-penalty GD steps), chain split over the GPUs
+    argg = (Xl_, Yl_, 0.01, Nl, dl, sl, 60, ol, laml, 0.0, 0.05)
+    ga = O.group_ADMM_logistic_GD(*argg, return_state=True)
+    gb = g.group_ADMM_logistic_GD(*argg, backend="b200", dist=D, return_state=True)
+    assert ga[2] == gb[2], ("logistic GD", ga[2], gb[2])
+    np.testing.assert_allclose(ga[0], gb[0], rtol=1e-9)
+    assert ga[4]["inner_steps"] == gb[4]["inner_steps"], (ga[4]["inner_steps"], gb[4]["inner_steps"])
     # synthetic shards are drawn per global worker id: same problem for any number of ranks
     from gadmm_b200.engine.logistic_scaled import gadmm_logistic_scaled
     from gadmm_b200.parallel.runtime import SoloDist
