@@ -193,6 +193,9 @@ def GD_DGD_LAG(X, y, num_workers, num_feature, Hmax, num_iter, obj0, X_fede, y_f
     if b == "b200":
         return _engine().gd_dgd_lag(X, y, num_workers, num_feature, Hmax, num_iter, obj0, X_fede,
                                     y_fede, num_sample, **kw)
+    if b in ("nccl", "gloo"):
+        return _dist(b).gd_dgd_lag(X, y, num_workers, num_feature, Hmax, num_iter, obj0, X_fede,
+                                   y_fede, num_sample, **kw)
     return _oracle.GD_DGD_LAG(X, y, num_workers, num_feature, Hmax, num_iter, obj0, X_fede,
                               y_fede, num_sample, **kw)
 
@@ -204,6 +207,9 @@ def GD_DGD_LAG_logistic(X, y, num_workers, num_feature, Hmax, num_iter, X_fede, 
     if b == "b200":
         return _engine().gd_dgd_lag_logistic(X, y, num_workers, num_feature, Hmax, num_iter,
                                              X_fede, y_fede, num_sample, lam, accuracy, **kw)
+    if b in ("nccl", "gloo"):
+        return _dist(b).gd_dgd_lag_logistic(X, y, num_workers, num_feature, Hmax, num_iter,
+                                            X_fede, y_fede, num_sample, lam, accuracy, **kw)
     return _oracle.GD_DGD_LAG_logistic(X, y, num_workers, num_feature, Hmax, num_iter, X_fede,
                                        y_fede, num_sample, lam, accuracy, **kw)
 
@@ -215,6 +221,9 @@ def dual_averaging(XX, YY, no_workers, num_feature, noSamples, num_iter, obj0, a
     if b == "b200":
         return _engine().dual_averaging(XX, YY, no_workers, num_feature, noSamples, num_iter,
                                         obj0, acc, alpha, **kw)
+    if b in ("nccl", "gloo"):
+        return _dist(b).dual_averaging(XX, YY, no_workers, num_feature, noSamples, num_iter,
+                                       obj0, acc, alpha, **kw)
     return _oracle.dual_averaging(XX, YY, no_workers, num_feature, noSamples, num_iter, obj0, acc,
                                   alpha, **kw)
 
@@ -226,6 +235,9 @@ def dual_averaging_logisticReg(XX, YY, no_workers, num_feature, noSamples, num_i
     if b == "b200":
         return _engine().dual_averaging_logistic(XX, YY, no_workers, num_feature, noSamples,
                                                  num_iter, obj0, acc, alpha, eta, **kw)
+    if b in ("nccl", "gloo"):
+        return _dist(b).dual_averaging_logistic(XX, YY, no_workers, num_feature, noSamples,
+                                                num_iter, obj0, acc, alpha, eta, **kw)
     return _oracle.dual_averaging_logisticReg(XX, YY, no_workers, num_feature, noSamples,
                                               num_iter, obj0, acc, alpha, eta, **kw)
 

@@ -14,7 +14,10 @@ from ..models.problems import LinearProblem, LogisticProblem, logistic_gradient
 from .gadmm import _Timer, _finish
 
 
-def _dual_avg(N, d, grad_fn, obj_fn, num_iter, obj0, acc, alpha, mode):
+def _dual_avg(N, d, grad_fn, obj_fn, num_iter, obj0, acc, alpha, mode, grads_all=None):
+    """``grads_all(theta) -> (N, d)``, when given, supplies every worker's gradient at the start of
+    the sweep instead of ``grad_fn(n, theta_n)`` inside it -- the same values, since worker n's
+    model is not touched before its own step (used by the distributed backends)."""
     theta = np.zeros((d, N))
     Zp = np.zeros((d, N))
     obj, loss = [], []
@@ -22,9 +25,10 @@ def _dual_avg(N, d, grad_fn, obj_fn, num_iter, obj0, acc, alpha, mode):
     Iter = num_iter
     for i in range(1, num_iter + 1):
         src = Zp if mode == "faithful" else Zp.copy()
+        Gall = grads_all(theta) if grads_all is not None else None
         for n in range(N):
             t0 = time.perf_counter()
-            g = grad_fn(n, theta[:, n])
+            g = Gall[n] if Gall is not None else grad_fn(n, theta[:, n])
             if N == 1:
                 z = g.copy()
             elif n == 0:

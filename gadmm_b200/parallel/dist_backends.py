@@ -78,5 +78,23 @@ class _Backend:
         return star_admm(XX, YY, rho, N, d, s, num_iter, obj0, acc, backend=self.name)
 
 
+    # first-order baselines: workers split over the ranks, all_gather / all_reduce only
+    def gd_dgd_lag(self, *a, **kw):
+        from .dist_first_order import gd_dgd_lag
+        return gd_dgd_lag(*a, backend=self.name, **kw)
+
+    def gd_dgd_lag_logistic(self, *a, **kw):
+        from .dist_first_order import gd_dgd_lag_logistic
+        return gd_dgd_lag_logistic(*a, backend=self.name, **kw)
+
+    def dual_averaging(self, *a, **kw):
+        from .dist_first_order import dual_averaging
+        return dual_averaging(*a, backend=self.name, **kw)
+
+    def dual_averaging_logistic(self, *a, **kw):
+        from .dist_first_order import dual_averaging_logistic
+        return dual_averaging_logistic(*a, backend=self.name, **kw)
+
+
 def get(name: str) -> _Backend:
     return _Backend(name)

@@ -37,6 +37,34 @@ def run(rank, world, port, q):
     b = g.standared_ADMM(XX, YY, 1.0, 24, 50, 50, 2000, obj0, 1e-4, backend="gloo")
     assert a[2] == b[2]
     np.testing.assert_allclose(a[0], b[0], rtol=1e-9)
+    # first-order baselines with the workers split over the two ranks (all_gather / all_reduce)
+    rb = np.random.default_rng(3)
+    Nb, sb, db = 7, 12, 9
+    Xb = rb.standard_normal((Nb * sb, db))
+    Yb = Xb @ rb.standard_normal(db) + 0.1 * rb.standard_normal(Nb * sb)
+    Xl = [Xb[i * sb:(i + 1) * sb] for i in range(Nb)]
+    yl = [Yb[i * sb:(i + 1) * sb] for i in range(Nb)]
+    Hm = np.array([np.linalg.eigvalsh(x.T @ x)[-1] for x in Xl])
+    ob = O.opt_sol_closedForm(Xb, Yb)
+    argsb = (Xl, yl, Nb, db, Hm, 120, ob, Xb, Yb, sb)
+    ra = O.GD_DGD_LAG(*argsb, rng=5)
+    rb2 = g.GD_DGD_LAG(*argsb, rng=5, backend="gloo")
+    for k in (0, 3, 6, 10, 14, 16):
+        np.testing.assert_allclose(ra[k], rb2[k], rtol=1e-9, atol=1e-12, err_msg=f"baseline {k}")
+    np.testing.assert_array_equal(ra[9], rb2[9])
+    np.testing.assert_array_equal(ra[13], rb2[13])
+    da = O.dual_averaging(Xb, Yb, Nb, db, sb, 80, ob, 1e-6, ra[18])
+    db2 = g.dual_averaging(Xb, Yb, Nb, db, sb, 80, ob, 1e-6, ra[18], backend="gloo")
+    assert da[2] == db2[2]
+    np.testing.assert_allclose(da[0], db2[0], rtol=1e-10)
+    Yc = np.where(Yb > 0, 1.0, -1.0)
+    ylc = [Yc[i * sb:(i + 1) * sb] for i in range(Nb)]
+    Hl = 0.25 * Hm + 1e-2
+    argsl = (Xl, ylc, Nb, db, Hl, 60, Xb, Yc, sb, 1e-2, 1e-9)
+    la = O.GD_DGD_LAG_logistic(*argsl, rng=2)
+    lb = g.GD_DGD_LAG_logistic(*argsl, rng=2, backend="gloo")
+    for k in (0, 3, 6, 10, 14, 16):
+        np.testing.assert_allclose(la[k], lb[k], rtol=1e-9, atol=1e-12, err_msg=f"logistic baseline {k}")
     dist.barrier()
     dist.destroy_process_group()
     q.put((rank, "ok", int(b[2])))

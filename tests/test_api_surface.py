@@ -38,6 +38,16 @@ def test_public_names_and_engine_targets():
         assert callable(getattr(g, name))
 
 
+def test_every_family_has_a_torch_distributed_baseline():
+    """backend="nccl"/"gloo" covers the chain, star and first-order families (BASELINE.json: the
+    NCCL implementation of the same algorithms is the thing to beat)."""
+    from gadmm_b200.parallel import dist_backends
+    be = dist_backends.get("gloo")
+    for name in ("gadmm_closed_form", "static_gadmm", "dynamic_gadmm", "dynamic_gadmm_v0", "star_admm",
+                 "gd_dgd_lag", "gd_dgd_lag_logistic", "dual_averaging", "dual_averaging_logistic"):
+        assert callable(getattr(be, name)), name
+
+
 def test_engine_classes_expose_their_run_paths():
     from gadmm_b200.engine.chain import ChainEngine
     from gadmm_b200.engine.first_order import FirstOrder
