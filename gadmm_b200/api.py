@@ -140,6 +140,9 @@ def group_ADMM_logistic(XX, YY, rho, no_workers, num_feature, per_samples, num_i
     kw.pop("newton_tol", None)
     kw.pop("solver", None)
     kw.pop("dist", None)
+    if b in ("nccl", "gloo"):
+        return _dist(b).gadmm_logistic(XX, YY, rho, no_workers, num_feature, per_samples, num_iter,
+                                       obj0, lambda_logistic, acc, **kw)
     return _oracle.group_ADMM_logistic(XX, YY, rho, no_workers, num_feature, per_samples,
                                        num_iter, obj0, lambda_logistic, acc, **kw)
 
@@ -151,6 +154,10 @@ def group_ADMM_logistic_GD(XX, YY, rho, no_workers, num_feature, per_samples, nu
     if b == "b200":
         return _engine().gadmm_logistic_gd(XX, YY, rho, no_workers, num_feature, per_samples,
                                            num_iter, obj0, lambda_logistic, acc, gdStep, **kw)
+    kw.pop("dist", None)
+    if b in ("nccl", "gloo"):
+        return _dist(b).gadmm_logistic_gd(XX, YY, rho, no_workers, num_feature, per_samples,
+                                          num_iter, obj0, lambda_logistic, acc, gdStep, **kw)
     return _oracle.group_ADMM_logistic_GD(XX, YY, rho, no_workers, num_feature, per_samples,
                                           num_iter, obj0, lambda_logistic, acc, gdStep, **kw)
 

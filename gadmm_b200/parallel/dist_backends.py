@@ -96,5 +96,15 @@ class _Backend:
         return dual_averaging_logistic(*a, backend=self.name, **kw)
 
 
+    # logistic GADMM: oracle local solvers per rank, all_gather of the model matrix per colour
+    def gadmm_logistic(self, *a, **kw):
+        from .dist_logistic import group_admm_logistic
+        return group_admm_logistic(*a, backend=self.name, **kw)
+
+    def gadmm_logistic_gd(self, *a, **kw):
+        from .dist_logistic import group_admm_logistic_gd
+        return group_admm_logistic_gd(*a, backend=self.name, **kw)
+
+
 def get(name: str) -> _Backend:
     return _Backend(name)

@@ -65,6 +65,17 @@ def run(rank, world, port, q):
     lb = g.GD_DGD_LAG_logistic(*argsl, rng=2, backend="gloo")
     for k in (0, 3, 6, 10, 14, 16):
         np.testing.assert_allclose(la[k], lb[k], rtol=1e-9, atol=1e-12, err_msg=f"logistic baseline {k}")
+    # logistic GADMM (exact and inexact local solves), chain split over the two ranks
+    star = O.opt_sol_logistic(Xb, Yc, db, 1e-3, Nb)
+    ea = O.group_ADMM_logistic(Xb, Yc, 5.0, Nb, db, sb, 25, star, 1e-3, 1e-3)
+    eb = g.group_ADMM_logistic(Xb, Yc, 5.0, Nb, db, sb, 25, star, 1e-3, 1e-3, backend="gloo")
+    assert ea[2] == eb[2]
+    np.testing.assert_allclose(ea[0], eb[0], rtol=1e-11)
+    ia = O.group_ADMM_logistic_GD(Xb, Yc, 0.01, Nb, db, sb, 20, star, 1e-3, 0.0, 0.05, return_state=True)
+    ib = g.group_ADMM_logistic_GD(Xb, Yc, 0.01, Nb, db, sb, 20, star, 1e-3, 0.0, 0.05, backend="gloo",
+                                  return_state=True)
+    assert ia[4]["inner_steps"] == ib[4]["inner_steps"]
+    np.testing.assert_allclose(ia[0], ib[0], rtol=1e-11)
     dist.barrier()
     dist.destroy_process_group()
     q.put((rank, "ok", int(b[2])))

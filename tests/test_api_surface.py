@@ -44,7 +44,8 @@ def test_every_family_has_a_torch_distributed_baseline():
     from gadmm_b200.parallel import dist_backends
     be = dist_backends.get("gloo")
     for name in ("gadmm_closed_form", "static_gadmm", "dynamic_gadmm", "dynamic_gadmm_v0", "star_admm",
-                 "gd_dgd_lag", "gd_dgd_lag_logistic", "dual_averaging", "dual_averaging_logistic"):
+                 "gd_dgd_lag", "gd_dgd_lag_logistic", "dual_averaging", "dual_averaging_logistic",
+                 "gadmm_logistic", "gadmm_logistic_gd"):
         assert callable(getattr(be, name)), name
 
 

@@ -57,3 +57,21 @@ def test_gloo_single_process_logistic_matches_oracle():
     db = g.dual_averaging_logisticReg(XX, YY, N, d, s, 60, star, 1e-9, a[18], lam, backend="gloo")
     assert da[2] == db[2]
     np.testing.assert_allclose(da[0], db[0], rtol=1e-10)
+
+
+def test_gloo_single_process_logistic_gadmm_matches_oracle():
+    rng = np.random.default_rng(4)
+    N, s, d, lam = 5, 14, 6, 1e-3
+    XX = rng.standard_normal((N * s, d))
+    YY = np.where(rng.standard_normal(N * s) > 0, 1.0, -1.0)
+    star = O.opt_sol_logistic(XX, YY, d, lam, N)
+    a = O.group_ADMM_logistic(XX, YY, 5.0, N, d, s, 40, star, lam, 1e-3, return_state=True)
+    b = g.group_ADMM_logistic(XX, YY, 5.0, N, d, s, 40, star, lam, 1e-3, backend="gloo", return_state=True)
+    assert a[2] == b[2]
+    np.testing.assert_allclose(a[0], b[0], rtol=1e-12)
+    np.testing.assert_allclose(a[4]["theta"], b[4]["theta"], rtol=1e-10, atol=1e-14)
+    a = O.group_ADMM_logistic_GD(XX, YY, 0.01, N, d, s, 30, star, lam, 0.0, 0.05, return_state=True)
+    b = g.group_ADMM_logistic_GD(XX, YY, 0.01, N, d, s, 30, star, lam, 0.0, 0.05, backend="gloo",
+                                 return_state=True)
+    assert a[2] == b[2] and a[4]["inner_steps"] == b[4]["inner_steps"]
+    np.testing.assert_allclose(a[0], b[0], rtol=1e-12)
