@@ -108,10 +108,22 @@ def main():
     # synthetic shards are drawn per global worker id: same problem for any number of ranks
     from gadmm_b200.engine.logistic_scaled import gadmm_logistic_scaled
     from gadmm_b200.parallel.runtime import SoloDist
-    sa = gadmm_logistic_scaled(8, 256, 64, 0.5, 1e-3, 12, 0.0, dist=D, return_state=True)
-    sb = gadmm_logistic_scaled(8, 256, 64, 0.5, 1e-3, 12, 0.0, dist=SoloDist(), return_state=True)
-    assert abs(sa[4]["obj0"] - sb[4]["obj0"]) <= 1e-9 * abs(sb[4]["obj0"])
-    np.testing.assert_allclose(sa[0], sb[0], rtol=1e-8)
+    syn_a = gadmm_logistic_scaled(8, 256, 64, 0.5, 1e-3, 12, 0.0, dist=D, return_state=True)
+    syn_b = gadmm_logistic_scaled(8, 256, 64, 0.5, 1e-3, 12, 0.0, dist=SoloDist(), return_state=True)
+    assert abs(syn_a[4]["obj0"] - syn_b[4]["obj0"]) <= 1e-9 * abs(syn_b[4]["obj0"])
+    np.testing.assert_allclose(syn_a[0], syn_b[0], rtol=1e-8)
+    # plain torch.distributed (NCCL) baselines of the first-order and logistic families
+    nb = g.GD_DGD_LAG(*argsb, rng=3, backend="nccl")
+    for kk in (0, 3, 6, 10, 14, 16):
+        np.testing.assert_allclose(ra[kk], nb[kk], rtol=1e-8, atol=1e-10, err_msg=f"nccl baseline {kk}")
+    np.testing.assert_array_equal(ra[9][:live], nb[9][:live])
+    dn = g.dual_averaging(Xb, Yb, Nb, db, sb, 300, ob, 1e-4, ra[18], backend="nccl")
+    do = O.dual_averaging(Xb, Yb, Nb, db, sb, 300, ob, 1e-4, ra[18])
+    assert dn[2] == do[2]
+    np.testing.assert_allclose(do[0], dn[0], rtol=1e-9)
+    ln = g.group_ADMM_logistic_GD(*argg, backend="nccl", return_state=True)
+    assert ln[4]["inner_steps"] == ga[4]["inner_steps"]
+    np.testing.assert_allclose(ga[0], ln[0], rtol=1e-10)
     # optional protocol stress: GADMM_STRESS_ITERS iterations, a new random
     # chain every iteration (drawn and switched on the device), split run == single-GPU run
     stress = int(os.environ.get("GADMM_STRESS_ITERS", "0"))
