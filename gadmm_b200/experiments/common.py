@@ -27,6 +27,7 @@ def add_common_args(ap: argparse.ArgumentParser):
     ap.add_argument("--seed", type=int, default=0)
     ap.add_argument("--quick", action="store_true", help="shrink iteration caps (smoke run)")
     ap.add_argument("--data-dir", default=None, help="directory holding dataNN/{data,y}.txt")
+    ap.add_argument("--fig", default=None, help="write the reference's semilogy figure as an .svg file")
 
 
 def apply_overrides(cfg, args):
@@ -47,9 +48,12 @@ def dataset_or_surrogate(data_dir, name, n_rows, n_cols, rng, labels=False):
     return X, y, True
 
 
-def finish(curves: Dict[str, np.ndarray], out, summary: dict):
+def finish(curves: Dict[str, np.ndarray], out, summary: dict, fig=None):
     if out:
         save_curves(out, curves)
+    if fig:
+        from ..plot import figure_from_curves
+        figure_from_curves(curves, fig, title=str(summary.get("driver", "")))
     print(json.dumps(summary))
     return curves
 

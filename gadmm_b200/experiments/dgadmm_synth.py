@@ -83,7 +83,7 @@ def main(argv=None):
     if a.quick:
         cfg.num_workers, cfg.n_topologies, cfg.num_iter = 24, 600, 3000
     curves, summary = run(cfg)
-    return finish(curves, a.out, summary)
+    return finish(curves, a.out, summary, a.fig)
 
 
 if __name__ == "__main__":

@@ -58,7 +58,7 @@ def main(argv=None):
     if a.quick:
         cfg.num_iter_baselines = 2000
     curves, summary = run(cfg)
-    return finish(curves, a.out, summary)
+    return finish(curves, a.out, summary, a.fig)
 
 
 if __name__ == "__main__":

@@ -71,7 +71,7 @@ def main(argv=None):
     if a.quick:
         cfg.num_iter_baselines, cfg.num_iter_dualavg = 5000, 2000
     curves, summary = run(cfg)
-    return finish(curves, a.out, summary)
+    return finish(curves, a.out, summary, a.fig)
 
 
 if __name__ == "__main__":

@@ -44,3 +44,25 @@ def test_dgadmm_synth_and_vs_admm():
     c, s = gadmm_vs_admm.run(gadmm_vs_admm.Config(num_workers=8, num_sample=12, num_iter=4000,
                                                   taus=(10,), backend="oracle"))
     assert s["cost_star"] > 0 and c["cumulative_com_ADMM"][0] == s["cost_star"]
+
+
+def test_svg_figure_from_driver_curves(tmp_path):
+    """--fig writes the reference's semilogy panels as a plain SVG (no plotting package needed)."""
+    import xml.dom.minidom
+    from gadmm_b200.experiments import linreg_synth
+    fig = tmp_path / "fig.svg"
+    curves = linreg_synth.main(["--backend", "oracle", "--quick", "--fig", str(fig)])
+    txt = fig.read_text()
+    xml.dom.minidom.parseString(txt)                       # well-formed
+    assert txt.count("<polyline") >= 8                     # baselines + 3 GADMM curves, 3 panels
+    assert "cumulative communication cost" in txt and "clock time" in txt
+    assert "loss_GADMM_rho3" in curves
+
+
+def test_svg_writer_handles_degenerate_series(tmp_path):
+    import numpy as np
+    from gadmm_b200.plot import save_semilogy_svg
+    p = save_semilogy_svg(str(tmp_path / "x.svg"), [
+        {"series": {"zero": ([1, 2, 3], [0.0, 0.0, 0.0]), "one": ([1], [2.0]),
+                    "nan": ([1, 2], [np.nan, 1e-3])}, "xlabel": "it", "logx": True}])
+    assert open(p).read().startswith("<svg")
