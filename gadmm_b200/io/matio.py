@@ -81,3 +81,63 @@ def save_curves(path: str, curves: dict):
                                       for k in keys])
     else:
         raise ValueError(f"unsupported curve format {ext!r}")
+
+
+_STATE_ARRAYS = ("theta", "dual", "path", "obj", "loss", "time")
+
+
+def save_state(path: str, state: dict):
+    """Write a solver checkpoint (``return_state=True`` / ``ChainEngine.state()``: ``theta`` d x N,
+    ``dual`` d x N, ``iteration``, optional ``path`` and curves so far) as ``.mat`` (v5), ``.npz``
+    or ``.pt`` by extension.  The reference keeps this state in function locals and never saves
+    it (``%save`` is commented out, GD_DGD_LAG.m:29); SURVEY.md section 5.4."""
+    ext = os.path.splitext(path)[1].lower()
+    rec = {}
+    for k, v in state.items():
+        if v is None:
+            continue
+        rec[k] = np.asarray(v, dtype=np.int64 if k == "path" else np.float64) \
+            if k in _STATE_ARRAYS or isinstance(v, np.ndarray) else v
+    if ext == ".mat":
+        sio.savemat(path, {k: (np.atleast_2d(v) if isinstance(v, np.ndarray) else v)
+                           for k, v in rec.items()}, format="5")
+    elif ext == ".npz":
+        np.savez(path, **rec)
+    elif ext == ".pt":
+        import torch
+        torch.save({k: (torch.from_numpy(np.ascontiguousarray(v)) if isinstance(v, np.ndarray) else v)
+                    for k, v in rec.items()}, path)
+    else:
+        raise ValueError(f"unsupported checkpoint format {ext!r}")
+    return path
+
+
+def load_state(path: str) -> dict:
+    """Inverse of :func:`save_state`: arrays come back as float64 (``path`` as int64, 1-based as
+    the solvers return it), scalars as Python numbers; pass the result as ``state=``."""
+    ext = os.path.splitext(path)[1].lower()
+    if ext == ".mat":
+        raw = {k: v for k, v in sio.loadmat(path).items() if not k.startswith("__")}
+    elif ext == ".npz":
+        with np.load(path, allow_pickle=False) as z:
+            raw = {k: z[k] for k in z.files}
+    elif ext == ".pt":
+        import torch
+        raw = {k: (v.numpy() if hasattr(v, "numpy") else v)
+               for k, v in torch.load(path, weights_only=True).items()}
+    else:
+        raise ValueError(f"unsupported checkpoint format {ext!r}")
+    out = {}
+    for k, v in raw.items():
+        a = np.asarray(v)
+        if k in ("theta", "dual"):
+            out[k] = np.ascontiguousarray(a, dtype=np.float64)   # MAT files come back column-major
+        elif k == "path":
+            out[k] = np.asarray(a, dtype=np.int64).reshape(-1)
+        elif a.ndim == 0 or a.size == 1:
+            x = a.reshape(-1)[0]
+            out[k] = int(x) if float(x).is_integer() and k in ("iteration", "inner_steps", "launches", "g0") \
+                else float(x)
+        else:
+            out[k] = np.asarray(a, dtype=np.float64).reshape(-1) if a.ndim <= 2 and 1 in a.shape else a
+    return out

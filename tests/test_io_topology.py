@@ -94,3 +94,26 @@ def test_comm_accounting():
     np.testing.assert_allclose(with_rechain_overhead([3.0]), [4.0])
     np.testing.assert_array_equal(energy_cumulative(2.0, 3), [2, 4, 6])
     assert iterations_to([1, 0.5, 1e-5, 1e-6], 1e-4) == 3
+
+
+def test_checkpoint_files_resume_exactly(tmp_path):
+    """save_state / load_state (.mat, .npz, .pt): a run resumed from the file continues the
+    uninterrupted run bit for bit."""
+    import numpy as np
+    from gadmm_b200 import io, oracle as O
+    rng = np.random.default_rng(2)
+    N, s, d = 6, 10, 8
+    XX, YY = rng.standard_normal((N * s, d)), rng.standard_normal(N * s)
+    obj0 = O.opt_sol_closedForm(XX, YY)
+    path0 = np.arange(1, N + 1)
+    args = (XX, YY, 2.0, N, d, s)
+    full = O.dynamic_group_ADMM_closedForm(*args, 60, obj0, 0.0, path0, np.ones(N - 1), 1e9)
+    part = O.dynamic_group_ADMM_closedForm(*args, 25, obj0, 0.0, path0, np.ones(N - 1), 1e9,
+                                           return_state=True)
+    for ext in (".mat", ".npz", ".pt"):
+        f = str(tmp_path / ("ckpt" + ext))
+        io.save_state(f, part[-1])
+        st = io.load_state(f)
+        assert st["iteration"] == 25 and st["theta"].shape == (d, N) and st["path"].tolist() == path0.tolist()
+        rest = O.dynamic_group_ADMM_closedForm(*args, 35, obj0, 0.0, path0, np.ones(N - 1), 1e9, state=st)
+        np.testing.assert_array_equal(np.concatenate([part[0], rest[0]]), full[0])
