@@ -73,7 +73,9 @@ def build(force: bool = False, verbose: bool = False, ptxas_info: bool = False) 
         if p.returncode != 0:
             raise RuntimeError(f"nvcc failed on {src}:\n{text}")
     tmp = lib_path() + ".tmp"
-    cmd = [nvcc, "-shared", "--cudart", "shared", "-o", tmp] + objs
+    # the arch flag keeps nvcc's link step from adding an (empty) cubin for its default sm_52
+    cmd = [nvcc, "-shared", "--cudart", "shared", "-gencode", "arch=compute_100a,code=sm_100a",
+           "-o", tmp] + objs
     r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT)
     if r.returncode != 0:
         raise RuntimeError("link failed:\n" + r.stdout.decode(errors="replace"))
