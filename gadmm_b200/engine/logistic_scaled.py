@@ -154,6 +154,7 @@ class ScaledLogisticGadmm:
         self.cvec = (self.hasL + self.hasR).squeeze(1)
         self.stats = {}
         self._last_loss = {}
+        self._last_eval = {}       # colour -> (X'w, loss) of the last accepted evaluation
         self.launches = 0
         self._scratch = None
         self._scratch_key = None
@@ -201,6 +202,7 @@ class ScaledLogisticGadmm:
 
         x0 = torch.zeros((1, self.d), dtype=torch.float64, device=self.dev)
         x, f, _ = newton_cg(evaluate, hessvec, x0, tol=tol, max_cg=2000)
+        self._last_eval.clear()            # the curvature state now belongs to the consensus point
         return float(f.item()), x[0]
 
     # ------------------------------------------------------------------ GADMM
@@ -213,7 +215,7 @@ class ScaledLogisticGadmm:
         if reuse and all(c in self._last_loss for c in (0, 1)):
             data = self._last_loss[0].sum() + self._last_loss[1].sum()
         else:
-            _, loss = self._xtwx(th, 0, self.Nloc, 1, 0)
+            _, loss = self._xtwx(th, 0, self.Nloc, 1, 0)      # same points: curvature state unchanged
             data = loss.sum()
         part = (data + 0.5 * self.lam_log * (th * th).sum()).reshape(1)
         self.dist.all_reduce_sum_(part)
@@ -244,8 +246,18 @@ class ScaledLogisticGadmm:
             lin -= rho * (left + right)
             mu = (self.lam_log + self.cvec[idx] * rho).unsqueeze(1)
 
+            fresh = {"first": True}
+
             def evaluate(x):
-                v, loss = self._xtwx(x.contiguous(), first, count, 2, 0)
+                # The data terms at the starting point are those of this colour's last accepted
+                # evaluation one iteration ago (its models have not moved since, and the curvature
+                # state of its shards is still in place): the first evaluation costs no pass.
+                if fresh["first"] and colour in self._last_eval:
+                    v, loss = self._last_eval[colour]
+                else:
+                    v, loss = self._xtwx(x.contiguous(), first, count, 2, 0)
+                    self._last_eval[colour] = (v, loss)
+                fresh["first"] = False
                 self._last_loss[colour] = loss
                 f = loss + 0.5 * mu.squeeze(1) * (x * x).sum(1) + (lin * x).sum(1)
                 return f, v + mu * x + lin
