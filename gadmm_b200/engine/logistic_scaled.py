@@ -37,7 +37,9 @@ def _pick_ctas_per_shard(n_shards: int, s: int, rb: int = 2) -> int:
         if g * rb * 4 > s and g > 1:
             break
         waves = -(-n_shards * g // _SM_COUNT)
-        cost = waves / g
+        # every CTA writes (and the reduction re-reads) a d-vector of partial sums: 16 g d bytes per
+        # shard against 4 s d bytes of shard data
+        cost = waves / g * (1.0 + 4.0 * g / max(s, 1))
         if best_cost is None or cost < best_cost * (1 - 1e-9):
             best, best_cost = g, cost
     return best
