@@ -64,6 +64,8 @@ def main():
         st = eng.state()
         out.update({"iterations": int(it), "acc": acc, "reached": bool(loss[-1] < acc), "final_gap": float(loss[-1]),
                     "time_s": float(tv[-1]), "s_per_iter": float(tv[-1] / max(len(tv), 1)),
+                    "first_iter_s": float(tv[0]),
+                    "s_per_iter_steady": float((tv[-1] - tv[0]) / max(len(tv) - 1, 1)),
                     "hessvecs": st.get("hessvecs"), "evals": st.get("evals"), "launches": st["launches"]})
     if D.rank == 0:
         print(json.dumps(out))

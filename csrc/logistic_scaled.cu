@@ -58,6 +58,11 @@ logistic_xtwx_kernel(const float* __restrict__ X, const double* __restrict__ y,
   double acc[LS_MAXC];
 #pragma unroll
   for (int c = 0; c < LS_MAXC; ++c) acc[c] = 0.0;
+  // fp64 modes are bound by the fp32->fp64 conversions (quarter-rate pipe).  With two rows per
+  // block the converted block fits in registers between the two phases (a thread touches the same
+  // columns in both), which halves the conversions and the shared-memory reads.
+  constexpr bool KEEP = !FAST && LS_RB == 2;
+  double keep[KEEP ? LS_RB : 1][KEEP ? LS_MAXC : 1];
   double loss = 0.0;
   const int nblk = (s + LS_RB - 1) / LS_RB;                 // row blocks of the shard
   const int mine = (nblk - g + G - 1) / G;                  // blocks g, g+G, ... handled here
@@ -114,10 +119,15 @@ logistic_xtwx_kernel(const float* __restrict__ X, const double* __restrict__ y,
 #pragma unroll
           for (int r = 0; r < LS_RB; ++r) {
             const float4 tv = *reinterpret_cast<const float4*>(t + (size_t)r * d + j);
-            dp[r] = fma((double)tv.x, xa.x, dp[r]);
-            dp[r] = fma((double)tv.y, xa.y, dp[r]);
-            dp[r] = fma((double)tv.z, xb.x, dp[r]);
-            dp[r] = fma((double)tv.w, xb.y, dp[r]);
+            const double t0 = (double)tv.x, t1 = (double)tv.y, t2 = (double)tv.z, t3 = (double)tv.w;
+            if constexpr (KEEP) {       // the column phase needs the same elements: convert once
+              keep[r][4 * c + 0] = t0; keep[r][4 * c + 1] = t1;
+              keep[r][4 * c + 2] = t2; keep[r][4 * c + 3] = t3;
+            }
+            dp[r] = fma(t0, xa.x, dp[r]);
+            dp[r] = fma(t1, xa.y, dp[r]);
+            dp[r] = fma(t2, xb.x, dp[r]);
+            dp[r] = fma(t3, xb.y, dp[r]);
           }
         }
       }
@@ -165,6 +175,16 @@ logistic_xtwx_kernel(const float* __restrict__ X, const double* __restrict__ y,
             }
           acc[4 * c + 0] += (double)a0; acc[4 * c + 1] += (double)a1;
           acc[4 * c + 2] += (double)a2; acc[4 * c + 3] += (double)a3;
+        } else if constexpr (KEEP) {
+#pragma unroll
+          for (int r = 0; r < LS_RB; ++r)
+            if (r < rows) {
+              const double w = wr[r];
+              acc[4 * c + 0] = fma(keep[r][4 * c + 0], w, acc[4 * c + 0]);
+              acc[4 * c + 1] = fma(keep[r][4 * c + 1], w, acc[4 * c + 1]);
+              acc[4 * c + 2] = fma(keep[r][4 * c + 2], w, acc[4 * c + 2]);
+              acc[4 * c + 3] = fma(keep[r][4 * c + 3], w, acc[4 * c + 3]);
+            }
         } else {
 #pragma unroll
           for (int r = 0; r < LS_RB; ++r)
