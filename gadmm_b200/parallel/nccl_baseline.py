@@ -11,7 +11,6 @@ None of the hand-written kernels are used here.
 from __future__ import annotations
 
 import time
-from typing import Optional
 
 import numpy as np
 import torch

@@ -4,7 +4,6 @@ Writes one JSON document; copy the numbers you want judged into profiles/."""
 import json
 import os
 import sys
-import time
 
 import torch
 
