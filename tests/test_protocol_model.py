@@ -114,3 +114,86 @@ def test_no_deadlock_all_workers_finish():
                 it[w] += 1
                 progress = True
     assert all(i == n_iter + 1 for i in it)
+
+
+# ------------------------------------------------------------------------------------------------
+# The per-iteration objective exchange (gadmm_dual_objective_kernel): every rank stores its partial
+# objective into slot ``it % RING`` of EVERY rank (entry = writer's rank), releases a flag per
+# destination, then waits for all ranks' flags ``>= it`` and reads their entries.  It doubles as the
+# bound on rank skew (nobody starts iteration it+1 before everybody has published iteration it).
+
+def _explore_ring(n_ranks: int, n_iter: int, ring: int, invariant=None):
+    """Returns (states_visited, violation or None); ``invariant(procs)`` is asserted in every
+    reachable state."""
+    # memory[dst][slot][src] = version (or -1 while torn), flag[dst][slot][src] = iteration
+    z = tuple(tuple(tuple(0 for _ in range(n_ranks)) for _ in range(ring)) for _ in range(n_ranks))
+    init = (tuple((1, 0) for _ in range(n_ranks)), z, z)
+    seen, stack = {init}, [init]
+
+    def put(a, dst, slot, src, val):
+        row = list(a[dst][slot])
+        row[src] = val
+        sl = list(a[dst])
+        sl[slot] = tuple(row)
+        return a[:dst] + (tuple(sl),) + a[dst + 1:]
+
+    while stack:
+        procs, mem, flg = stack.pop()
+        if invariant is not None:
+            invariant(procs)
+        enabled = 0
+        for r in range(n_ranks):
+            it, pc = procs[r]
+            if it > n_iter:
+                continue
+            slot = it % ring
+            nmem, nflg = mem, flg
+            if pc < 2 * n_ranks:                       # store to destination pc//2 in two steps
+                dst = pc // 2
+                nmem = put(mem, dst, slot, r, -1 if pc % 2 == 0 else it)
+                nxt = (it, pc + 1)
+            elif pc < 3 * n_ranks:                     # release the flag at each destination
+                dst = pc - 2 * n_ranks
+                nflg = put(flg, dst, slot, r, it)
+                nxt = (it, pc + 1)
+            else:                                      # wait for + read source q's entry here
+                q = pc - 3 * n_ranks
+                if flg[r][slot][q] < it:
+                    continue
+                got = mem[r][slot][q]
+                if got != it:
+                    return len(seen), (r, it, q, got)
+                nxt = (it, pc + 1) if q + 1 < n_ranks else (it + 1, 0)
+            enabled += 1
+            state = (procs[:r] + (nxt,) + procs[r + 1:], nmem, nflg)
+            if state not in seen:
+                seen.add(state)
+                stack.append(state)
+        if enabled == 0 and any(it <= n_iter for it, _ in procs):
+            return len(seen), ("deadlock", procs, None, None)
+    return len(seen), None
+
+
+@pytest.mark.parametrize("n_ranks,n_iter,ring", [(2, 6, 4), (3, 3, 4), (2, 6, 2)])
+def test_objective_exchange_ring_is_safe(n_ranks, n_iter, ring):
+    states, bad = _explore_ring(n_ranks, n_iter, ring)
+    assert bad is None, bad
+    assert states > 50
+
+
+def test_objective_exchange_needs_more_than_one_slot():
+    """Negative control: with a single slot a fast rank's next partial objective overwrites the one
+    a slower rank has not read yet (the flag only says 'written', not 'consumed')."""
+    _, bad = _explore_ring(2, 3, 1)
+    assert bad is not None and bad[0] != "deadlock"
+
+
+def test_objective_exchange_bounds_rank_skew():
+    """A rank finishes iteration it only after reading every rank's iteration-it entry, so in every
+    reachable state the ranks are at most one iteration apart."""
+    def skew(procs):
+        its = [it for it, _ in procs]
+        assert max(its) - min(its) <= 1, procs
+
+    _, bad = _explore_ring(3, 3, 4, invariant=skew)
+    assert bad is None
