@@ -46,8 +46,8 @@ def pairwise_sq_dist(x: np.ndarray, y: np.ndarray) -> np.ndarray:
 def greedy_chain(d_square: np.ndarray, start: int = 0):
     """Greedy nearest-neighbour chain (0-based) -- findPath.m:16-30.
 
-    Returns ``(path, hops)`` where ``hops[k]`` is the (from, to) pair of hop k.  The scan keeps the
-    reference's strict ``temp < min`` test with ``min = 1e12`` so ties resolve to the lowest index.
+    Returns the path as an int64 array.  The scan keeps the reference's strict ``temp < min`` test
+    with ``min = 1e12`` so ties resolve to the lowest index.
     """
     n_nodes = d_square.shape[0]
     visited = np.zeros(n_nodes, dtype=bool)
