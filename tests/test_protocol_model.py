@@ -197,3 +197,93 @@ def test_objective_exchange_bounds_rank_skew():
 
     _, bad = _explore_ring(3, 3, 4, invariant=skew)
     assert bad is None
+
+
+# ------------------------------------------------------------------------------------------------
+# D-GADMM: the whole iteration with a NEW chain every iteration (tau = 1), one worker per rank.
+# Per iteration a rank (1) pulls the latest models (version it-1) of its new neighbours straight out
+# of the owners' replicas (csrc/rechain.cu), (2) runs its half-iteration in the colour the new
+# chain gives it, (3) does the dual update, (4) takes part in the objective exchange.  The exchange
+# is the only thing that keeps a fast rank from overwriting slot (it-1)&1 while a slow rank still
+# pulls from it, so the composite model is checked with and without it.
+
+def _explore_dgadmm(chains, n_iter: int, with_exchange: bool):
+    n = len(chains[0])
+
+    def program(rank, it):
+        chain = chains[(it - 1) % len(chains)]
+        pos = chain.index(rank)
+        nb = [chain[p] for p in (pos - 1, pos + 1) if 0 <= p < n]
+        ops = [("read", q, it - 1, it - 1) for q in nb]                 # re-chain pull (flag >= it-1)
+        if pos % 2 == 1:                                                # tail: heads of THIS iteration
+            ops += [("read", q, it, it) for q in nb]
+        ops += [("wbegin",), ("wend",), ("release",)]
+        ops += [("read", q, it, it) for q in nb]                        # dual update
+        if with_exchange:
+            ops += [("xput", q) for q in range(n)] + [("xget", q) for q in range(n)]
+        return ops
+
+    theta0 = tuple((0, 0) for _ in range(n))                            # per owner: (slot0, slot1)
+    zero = tuple(0 for _ in range(n))
+    xz = tuple(tuple(0 for _ in range(n)) for _ in range(n))            # xflag[dst][src]
+    init = (tuple((1, 0) for _ in range(n)), theta0, zero, xz)
+    seen, stack = {init}, [init]
+    while stack:
+        procs, th, fl, xf = stack.pop()
+        enabled = 0
+        for r in range(n):
+            it, pc = procs[r]
+            if it > n_iter:
+                continue
+            ops = program(r, it)
+            op = ops[pc]
+            nth, nfl, nxf = th, fl, xf
+            if op[0] == "read":
+                _, q, need, expect = op
+                if fl[q] < need:
+                    continue
+                got = th[q][expect % 2]
+                if got != expect:
+                    return len(seen), (r, it, q, expect, got)
+            elif op[0] in ("wbegin", "wend"):
+                row = list(th[r])
+                row[it % 2] = -1 if op[0] == "wbegin" else it
+                nth = th[:r] + (tuple(row),) + th[r + 1:]
+            elif op[0] == "release":
+                nfl = fl[:r] + (it,) + fl[r + 1:]
+            elif op[0] == "xput":
+                row = list(xf[op[1]])
+                row[r] = it
+                nxf = xf[:op[1]] + (tuple(row),) + xf[op[1] + 1:]
+            elif op[0] == "xget":
+                if xf[r][op[1]] < it:
+                    continue
+            nxt = (it, pc + 1) if pc + 1 < len(ops) else (it + 1, 0)
+            enabled += 1
+            state = (procs[:r] + (nxt,) + procs[r + 1:], nth, nfl, nxf)
+            if state not in seen:
+                seen.add(state)
+                stack.append(state)
+        if enabled == 0 and any(it <= n_iter for it, _ in procs):
+            return len(seen), ("deadlock", procs, fl, None, None)
+    return len(seen), None
+
+
+_CHAINS3 = [[0, 1, 2], [1, 0, 2], [2, 1, 0], [0, 2, 1]]
+_CHAINS4 = [[0, 1, 2, 3], [0, 2, 1, 3], [3, 0, 2, 1], [1, 3, 0, 2]]
+
+
+@pytest.mark.parametrize("chains,n_iter", [(_CHAINS3, 4), (_CHAINS4, 3)])
+def test_dgadmm_rechain_every_iteration_is_safe_with_the_exchange(chains, n_iter):
+    states, bad = _explore_dgadmm(chains, n_iter, with_exchange=True)
+    assert bad is None, bad
+    assert states > 100
+
+
+def test_dgadmm_rechain_without_the_exchange_is_caught():
+    """Negative control: drop the per-iteration exchange and a rank that is two iterations ahead
+    overwrites the replica slot a slower rank is still reading (the checker finds a torn read of
+    rank 3's iteration-1 model while rank 3 writes iteration 3) -- the reason the stop-test
+    exchange stays on every iteration of a re-chained run."""
+    _, bad = _explore_dgadmm(_CHAINS4, 4, with_exchange=False)
+    assert bad is not None and bad[0] != "deadlock" and bad[4] == -1
