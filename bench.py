@@ -1,20 +1,31 @@
 #!/usr/bin/env python
-"""Headline benchmark: GADMM iterations/s on the scaled synthetic linear-regression config of
-BASELINE.json (1024 logical workers x d=4096, strong scaling over 1/2/4/8 GPUs).
+"""Headline benchmark: GADMM iterations/s and time to the 1e-4 objective gap on the scaled
+synthetic linear-regression config of BASELINE.json (1024 logical workers x d=4096, strong
+scaling over 1/2/4/8 GPUs).
 
 A "step" is one full GADMM iteration: head half-iteration, tail half-iteration, dual update,
 all-rank objective reduction and stop test (group_ADMM_closedForm.m:11-108).  The timed region
 is exactly K steps on the device (CUDA events, max over ranks).  Every step streams all packed
-inverses once (N*d^2/2 elements, 68.7 GB at the default config: far larger than the 126 MB L2,
+inverses once (N*d^2/2 elements, 69.8 GB at the default config: far larger than the 126 MB L2,
 so no L2 flush is needed between steps).
+
+One invocation measures, in this order:
+  1. the product arm (hand-written kernels, P2P flags): K timed steps, then the end-to-end
+     number through the public streaming API (`ChainEngine.step`: H2D control block from pinned
+     memory + kernels + D2H objective every step);
+  2. time / iterations to the 1e-4 gap on the same engine and data: D-GADMM with a new chain
+     every `--tau` iterations (chains drawn and built on the GPU) and static GADMM, where
+     "reached" means the gap stays below 1e-4 for the rest of the run;
+  3. the baseline arm BASELINE.json names -- torch ops + NCCL send/recv + all_reduce
+     (`gadmm_b200/parallel/nccl_baseline.py`, none of our kernels) -- for the same K steps, so
+     that `vs_baseline` = product iters/s / baseline iters/s is measured on the same box.
 
     python bench.py --gpus 1 --steps 20 --warmup 3
     python -m torch.distributed.run --nproc-per-node 8 ... bench.py --gpus 8 --steps 20 --warmup 3
     python bench.py --impl reference      # the MATLAB reference cannot run here -> "unavailable"
 """
 import argparse
-import os as _os
-_os.environ.pop("NCCL_DEBUG", None)   # NCCL prints its version banner on stdout otherwise
+import gc
 import json
 import os
 import sys
@@ -32,13 +43,17 @@ def parse():
     ap.add_argument("--workers", type=int, default=1024)
     ap.add_argument("--d", type=int, default=4096)
     ap.add_argument("--s", type=int, default=1024)
-    ap.add_argument("--rho", type=float, default=1.0)
+    ap.add_argument("--rho", type=float, default=10.0)
     ap.add_argument("--store", default="f64", choices=["f64", "f32"])
     ap.add_argument("--e2e-steps", type=int, default=0, help="0 = same as --steps")
     ap.add_argument("--verbose", action="store_true")
     ap.add_argument("--gram", default="f64", choices=["f64", "tc"],
                     help="setup Gram: fp64 SIMT or tcgen05 split-tf32 (sample-heavy shards)")
     ap.add_argument("--no-graph", action="store_true", help="launch kernels one by one")
+    ap.add_argument("--no-baseline", action="store_true", help="skip the in-process NCCL baseline arm")
+    ap.add_argument("--no-tta", action="store_true", help="skip the time-to-1e-4 runs")
+    ap.add_argument("--tau", type=int, default=10, help="D-GADMM re-chaining period of the tta run")
+    ap.add_argument("--tta-cap", type=int, default=320, help="iterations of each time-to-1e-4 run")
     return ap.parse_args()
 
 
@@ -51,48 +66,14 @@ def reference_arm(a):
     return 0
 
 
-def main():
-    a = parse()
-    if a.impl == "reference":
-        return reference_arm(a)
-    import numpy as np
+def timed_steps(eng, a, D, rank, local, graph):
+    """W untimed warm-up steps, then exactly K timed steps (CUDA events, max over ranks)."""
     import torch
-    import torch.distributed as dist
-    from gadmm_b200.parallel.runtime import Dist, init_process_group
     from gadmm_b200.utils import ClockSampler
-
-    rank, world, local = init_process_group("nccl")
-    if world != a.gpus and rank == 0:
-        print(f"warning: --gpus {a.gpus} but WORLD_SIZE={world}", file=sys.stderr)
-    torch.cuda.set_device(local)
-    D = Dist()
-    N, d, s = a.workers, a.d, a.s
-    t_setup0 = time.time()
-
-    if a.impl == "nccl":
-        from gadmm_b200.parallel.nccl_baseline import NcclChainGadmm as Engine
-        eng = Engine(N, d, a.rho, 0.0, 1e-4, a.warmup + 2 * a.steps + 8, dist=D)
-        from gadmm_b200.parallel.nccl_baseline import build_scaled_linreg
-    else:
-        from gadmm_b200.engine.chain import ChainEngine
-        from gadmm_b200.engine.scaled import build_scaled_linreg
-        es = a.e2e_steps or a.steps
-        eng = ChainEngine(N, d, a.rho, 0.0, 1e-4, a.warmup + 2 * a.steps + es + 8, dist=D,
-                          store=a.store, dynamic=False, stop=False)
-    kw = {"gram": a.gram} if a.impl == "b200" else {}
-    obj0 = build_scaled_linreg(eng, s, seed=0, verbose=a.verbose, **kw)
-    eng.set_path(np.arange(N))
-    torch.cuda.synchronize()
-    D.barrier()
-    setup_s = time.time() - t_setup0
-
-    # ---- warm-up (untimed), then exactly K timed steps; device clock, max over ranks
-    # The K-step window is captured once as a CUDA graph (3 kernels per step, device-resident
-    # iteration counter) and replayed; capture + first replay are part of the warm-up.
-    graph = not a.no_graph
-    eng.iterate(a.warmup, use_graph=False)
+    warm = max(3, a.warmup)
+    eng.iterate(warm, use_graph=False)
     if graph:
-        eng.iterate(a.steps, use_graph=True)
+        eng.iterate(a.steps, use_graph=True)     # capture + first replay belong to the warm-up
     torch.cuda.synchronize()
     D.barrier()
     sampler = ClockSampler(local)
@@ -111,32 +92,149 @@ def main():
     launches = getattr(eng, "launches", 0) - l0
     ms = D.all_reduce_max(e0.elapsed_time(e1))
     clocks = sampler.stop() if rank == 0 else None
+    done = warm + (2 if graph else 1) * a.steps
+    return ms, launches, clocks, done
+
+
+def first_stay_below(loss, acc):
+    """1-based iteration from which the gap stays below ``acc`` until the end of the run (0 = never)."""
+    import numpy as np
+    bad = np.nonzero(np.asarray(loss) >= acc)[0]
+    first = (int(bad[-1]) + 1 if bad.size else 0) + 1
+    return first if first <= len(loss) else 0
+
+
+def tta_runs(eng, a, D, N):
+    """Time / iterations to the 1e-4 gap, device clock from the end of iteration 1, max over
+    ranks.  The runs do not stop at the first crossing: the whole window is executed and the
+    gap has to *stay* below 1e-4."""
+    import numpy as np
+    from gadmm_b200.ops.topology import find_path_batch_device
+    out = {}
+    cap = int(a.tta_cap)
+    for name, tau in ((f"dgadmm_tau{a.tau}", a.tau), ("gadmm_static", 0)):
+        eng.reset(stop=False, acc=1e-4)
+        eng.set_path(np.arange(N))
+        if tau > 0:
+            def chunk_src(base, K):      # same seed on every rank -> same chains everywhere
+                return find_path_batch_device(K, N, seed=11, stream_id=base, device=D.device)[0]
+            it = eng.run_device_rechain(cap, None, tau, window=32, chunk=64, chunk_source=chunk_src)
+        else:
+            it = eng.run(cap, window=32)
+        obj, loss, it, tv = eng.results(it)
+        hit = first_stay_below(loss, 1e-4)
+        out[name] = {"reached": bool(hit), "iters_to_1e-4": hit or None,
+                     "time_to_1e-4_s": float(tv[hit - 1]) if hit else None,
+                     "iterations_run": int(it), "gap_at_end": float(loss[-1]),
+                     "ms_per_iter": 1e3 * float(tv[-1]) / max(int(it) - 1, 1)}
+    return out
+
+
+def product_arm(a, D, rank, world, local):
+    import numpy as np
+    import torch
+    from gadmm_b200.engine.chain import ChainEngine
+    from gadmm_b200.engine.scaled import build_scaled_linreg
+    N, d, s = a.workers, a.d, a.s
+    es = a.e2e_steps or a.steps
+    warm = max(3, a.warmup)
+    cap = max(warm + 2 * a.steps + es + 8, 0 if a.no_tta else a.tta_cap + 8)
+    t0 = time.time()
+    # dynamic=True keeps both inverses (c=1 and c=2) per worker so that the same engine also runs
+    # the D-GADMM time-to-accuracy measurement; a step streams one of them per worker either way
+    eng = ChainEngine(N, d, a.rho, 0.0, 1e-4, cap, dist=D, store=a.store, dynamic=not a.no_tta,
+                      stop=False)
+    obj0 = build_scaled_linreg(eng, s, seed=0, verbose=a.verbose, gram=a.gram)
+    eng.set_path(np.arange(N))
+    torch.cuda.synchronize()
+    D.barrier()
+    setup_s = time.time() - t0
+    graph = not a.no_graph
+    ms, launches, clocks, done = timed_steps(eng, a, D, rank, local, graph)
 
     # ---- end to end through the public streaming API: per step H2D control block from pinned
-    #      memory, 3 kernels, D2H (objective, loss); host wall clock, max over ranks
-    e2e = None
-    if a.impl == "b200":
-        es = a.e2e_steps or a.steps
-        eng.step()
-        D.barrier()
-        torch.cuda.synchronize()
-        t0 = time.perf_counter()
-        last = None
-        for _ in range(es):
-            last = eng.step()
-        torch.cuda.synchronize()
-        wall = D.all_reduce_max(time.perf_counter() - t0)
-        e2e = {"value": es / wall, "unit": "iters/s", "ms_per_step": 1e3 * wall / es,
-               "h2d_bytes_per_step": eng.step_h2d_bytes, "d2h_bytes_per_step": eng.step_d2h_bytes,
-               "last_loss": last[1]}
+    #      memory, the kernels, D2H (objective, loss); host wall clock, max over ranks
+    eng.step()
+    D.barrier()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    last = None
+    for _ in range(es):
+        last = eng.step()
+    torch.cuda.synchronize()
+    wall = D.all_reduce_max(time.perf_counter() - t0)
+    e2e = {"value": es / wall, "unit": "iters/s", "ms_per_step": 1e3 * wall / es,
+           "h2d_bytes_per_step": eng.step_h2d_bytes, "d2h_bytes_per_step": eng.step_d2h_bytes,
+           "last_loss": last[1]}
+    obj, loss, it, tv = eng.results(done)
+    tta = None
+    if not a.no_tta:
+        try:
+            tta = tta_runs(eng, a, D, N)
+        except Exception as e:          # the headline number must survive a failing extra
+            tta = {"error": repr(e)[:300]}
+    elt = 8 if a.store == "f64" else 4
+    nT = (d + 63) // 64
+    rec = {"ms": ms, "launches": launches, "clocks": clocks, "e2e": e2e, "setup_s": setup_s,
+           "obj0": obj0, "loss_first": float(loss[0]), "loss_last": float(loss[-1]), "tta": tta,
+           "bytes_per_step": N * (nT * (nT + 1) // 2) * 64 * 64 * elt}
+    del eng
+    gc.collect()
+    torch.cuda.empty_cache()
+    return rec
 
-    obj, loss, it, tv = eng.results(a.warmup + (2 if graph else 1) * a.steps)
+
+def nccl_arm(a, D, rank, world, local):
+    import numpy as np
+    import torch
+    from gadmm_b200.parallel.nccl_baseline import NcclChainGadmm, build_scaled_linreg
+    N, d, s = a.workers, a.d, a.s
+    t0 = time.time()
+    eng = NcclChainGadmm(N, d, a.rho, 0.0, 1e-4, max(3, a.warmup) + 2 * a.steps + 8, dist=D)
+    obj0 = build_scaled_linreg(eng, s, seed=0, verbose=a.verbose)
+    eng.set_path(np.arange(N))
+    torch.cuda.synchronize()
+    D.barrier()
+    setup_s = time.time() - t0
+    ms, launches, clocks, done = timed_steps(eng, a, D, rank, local, False)
+    obj, loss, it, tv = eng.results(done)
+    rec = {"ms": ms, "launches": launches, "clocks": clocks, "setup_s": setup_s, "obj0": obj0,
+           "loss_first": float(loss[0]), "loss_last": float(loss[-1]),
+           "bytes_per_step": N * d * d * 8}      # dense fp64 inverses through cuBLAS bmm
+    del eng
+    gc.collect()
+    torch.cuda.empty_cache()
+    return rec
+
+
+def main():
+    a = parse()
+    if a.impl == "reference":
+        return reference_arm(a)
+    import torch
+    import torch.distributed as dist
+    from gadmm_b200.parallel.runtime import Dist, init_process_group
+
+    rank, world, local = init_process_group("nccl")
+    if world != a.gpus and rank == 0:
+        print(f"warning: --gpus {a.gpus} but WORLD_SIZE={world}", file=sys.stderr)
+    torch.cuda.set_device(local)
+    D = Dist()
+    N, d, s = a.workers, a.d, a.s
+
+    base = None
+    if a.impl == "nccl":
+        main_rec = nccl_arm(a, D, rank, world, local)
+    else:
+        main_rec = product_arm(a, D, rank, world, local)
+        if not a.no_baseline:
+            try:
+                base = nccl_arm(a, D, rank, world, local)
+            except Exception as e:      # e.g. out of memory for the dense inverses
+                base = {"error": repr(e)[:300]}
+
     if rank == 0:
-        elt = 8 if a.store == "f64" else 4
-        nT = (d + 63) // 64
-        bytes_per_step = N * (nT * (nT + 1) // 2) * 64 * 64 * elt
-        if a.impl == "nccl":
-            bytes_per_step = N * d * d * 8       # dense fp64 inverses through cuBLAS bmm
+        ms = main_rec["ms"]
         peaks = {}
         try:
             peaks = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)),
@@ -144,28 +242,48 @@ def main():
         except Exception:
             pass
         hbm = peaks.get("hbm_gbs", 6650.0)
+        bytes_per_step = main_rec["bytes_per_step"]
         gbs = bytes_per_step / world / (ms / a.steps * 1e-3) / 1e9
+        value = a.steps / (ms * 1e-3)
+        baseline = None
+        vs = None
+        if base is not None and "error" not in base:
+            bval = a.steps / (base["ms"] * 1e-3)
+            vs = value / bval
+            baseline = {"impl": "nccl (torch bmm + NCCL send/recv + all_reduce, dense fp64 inverses; "
+                                "gadmm_b200/parallel/nccl_baseline.py)",
+                        "value": bval, "unit": "iters/s", "ms_per_step": base["ms"] / a.steps,
+                        "GB_per_step_per_gpu": base["bytes_per_step"] / world / 1e9,
+                        "loss_last": base["loss_last"], "setup_s": base["setup_s"],
+                        "clocks": base["clocks"]}
+        elif base is not None:
+            baseline = base
         out = {
             "metric": "GADMM iters/s (one iter = head + tail half-iterations + dual update + "
-                      "objective/stop test)",
-            "value": a.steps / (ms * 1e-3), "unit": "iters/s", "n_gpus": world, "steps": a.steps,
-            "warmup": a.warmup, "ms_per_step": ms / a.steps, "higher_is_better": True,
-            "scaling": "strong", "vs_baseline": None, "dtype": "fp64" if a.store == "f64"
-            else "fp32-storage/fp64-accumulate", "data": "synthetic", "impl": a.impl,
+                      "objective/stop test); time-to-1e-4 objective gap in `tta`",
+            "value": value, "unit": "iters/s", "n_gpus": world, "steps": a.steps,
+            "warmup": max(3, a.warmup), "ms_per_step": ms / a.steps, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": vs,
+            "vs_baseline_note": "BASELINE.md has no published number (MATLAB reference, not "
+                                "runnable here); the ratio is against the NCCL baseline arm "
+                                "BASELINE.json names, run in this same invocation (`baseline`)",
+            "dtype": "fp64" if a.store == "f64" else "fp32-storage/fp64-accumulate",
+            "data": "synthetic", "impl": a.impl,
             "config": {"model": "GADMM closed-form linear regression (group_ADMM_closedForm)",
                        "workers": N, "d": d, "samples_per_worker": s, "rho": a.rho, "setup_gram": a.gram,
                        "global_batch": N * s, "seq_len": d,
                        "parallelism": f"chain-segments x{world} (consensus DP)",
                        "l2": "inputs larger than L2: every step streams all packed inverses "
                              f"({bytes_per_step / 1e9:.1f} GB total)"},
-            "gpu_launches": launches, "clocks": clocks, "e2e": e2e,
-            "setup_s": setup_s, "obj0": obj0, "loss_first": float(loss[0]),
-            "loss_last": float(loss[-1]),
+            "gpu_launches": main_rec["launches"], "clocks": main_rec["clocks"],
+            "e2e": main_rec.get("e2e"), "tta": main_rec.get("tta"), "baseline": baseline,
+            "setup_s": main_rec["setup_s"], "obj0": main_rec["obj0"],
+            "loss_first": main_rec["loss_first"], "loss_last": main_rec["loss_last"],
             "roofline": {"algorithmic_GB_per_step_per_gpu": bytes_per_step / world / 1e9,
                          "achieved_GBps_per_gpu": gbs, "hbm_peak_GBps": hbm,
                          "frac_of_measured" if peaks else "frac_of_fallback": gbs / hbm},
         }
-        print(json.dumps(out))
+        print(json.dumps(out), flush=True)
     if world > 1:
         dist.destroy_process_group()
     return 0

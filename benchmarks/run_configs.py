@@ -18,7 +18,6 @@ import time
 import numpy as np
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-os.environ.pop("NCCL_DEBUG", None)
 
 
 def emit(D, **kw):

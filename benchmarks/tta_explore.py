@@ -3,7 +3,6 @@
 import argparse, json, os, sys, time
 import numpy as np
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-os.environ.pop("NCCL_DEBUG", None)
 
 
 def main():

@@ -114,6 +114,20 @@ __device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long
   asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
   return v;
 }
+__device__ __forceinline__ unsigned long long ld_acquire_gpu(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_gpu(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+// Same-GPU producer (another kernel or CTA of this process): device scope is enough.
+__device__ __forceinline__ void wait_flag_ge_gpu(const unsigned long long* p, unsigned long long want) {
+  while (ld_acquire_gpu(p) < want) {
+    __nanosleep(20);
+  }
+}
 // Spin until *p >= want.  `abort_flag` (may be null) lets the host break a wedged wait.
 __device__ __forceinline__ void wait_flag_ge(const unsigned long long* p, unsigned long long want) {
   while (ld_acquire_sys(p) < want) {

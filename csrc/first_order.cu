@@ -320,7 +320,8 @@ shared_server_kernel(const GadmmShared p) {
 // ------------------------------------------------------ chain halo + objective exchange (K8)
 // grid = 3 CTAs.  CTA 0: this GPU's objective partial -> every GPU's fx ring (P2P stores + release
 // flag), wait for all ranks, total -> ftot[it & 1] (same order everywhere -> same stop decision).
-// CTA 1 / CTA 2 (push_y): first / last local gradient row -> the left / right neighbour GPU's Ytab.
+// CTA 1 / CTA 2 (push_y): first / last local gradient row -> the left / right neighbour GPU's Ytab
+// (after the neighbour has posted its partial of this iteration, i.e. has consumed the old row).
 __global__ void __launch_bounds__(256)
 own_exchange_kernel(const GadmmOwn p, const int push_y) {
   __shared__ double red[32];
@@ -350,6 +351,12 @@ own_exchange_kernel(const GadmmOwn p, const int push_y) {
   const int gsrc = left ? p.gid0 : p.gid0 + p.N - 1;     // global row to publish
   const int peer = left ? p.rank - 1 : p.rank + 1;
   if (peer < 0 || peer >= p.nranks) return;
+  // Back-pressure: the peer's halo row is single-buffered, and its dgd_update(it-1) reads it.
+  // The peer posts its objective partial of iteration `it` (CTA 0 of this kernel over there) only
+  // after that update has completed in its stream, so waiting for the post makes the overwrite
+  // safe.  No cycle: the post does not depend on anything this GPU does in iteration `it`.
+  if (tid == 0) wait_flag_ge(p.fxflag + (size_t)(it & 1ull) * p.nranks + peer, it);
+  __syncthreads();
   const double* src = p.Ytab + (size_t)gsrc * dp;
   double* dst = p.Ytab_peer[peer] + (size_t)gsrc * dp;
   for (int j = tid; j < dp; j += 256) dst[j] = src[j];

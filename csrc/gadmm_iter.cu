@@ -14,6 +14,17 @@
 //     (static_group_ADMM_closedForm.m:130-160; group_ADMM_closedForm.m:96-108)
 //
 // No NCCL and no host on this path: consumers spin on `flags` with ld.acquire.sys.
+//
+// Windows.  gadmm_chain_iterate() enqueues a *window* of iterations; every launch carries its
+// offset inside the window and works on iteration sync[0] + offset (sync[0] is set from ctrl[0]
+// by gadmm_window_begin_kernel, the window's first, fully stream-ordered launch).  That makes
+// every other launch of the window -- the next iteration's head phase included -- eligible for
+// programmatic dependent launch: all ordering inside a window is by data (version flags of
+// theta, `nuflag` of the node duals, `sync[1]` = last iteration whose stop decision is final),
+// so the head phase of iteration i+1 fills SMs while the tail phase of iteration i drains and
+// while the all-rank objective exchange of iteration i is still in flight.  With the stop test
+// enabled the head phase of i+1 may therefore run speculatively after the test fired at i; it
+// only touches the other parity slot of theta, so the frozen state is the state of iteration i.
 #include "../include/gadmm_b200.h"
 #include "symv_core.cuh"
 
@@ -68,41 +79,78 @@ struct ChainX {
     double t = 0.0;
     if (tl) t += __ldcg(tl + j);
     if (tr) t += __ldcg(tr + j);
-    return fma(rho, t, b[j] - nu[j]);
+    return fma(rho, t, b[j] - __ldcg(nu + j));   // nu is rewritten by a kernel that may overlap
   }
 };
+
+// Common entry of every launch of a window: which iteration is this, and is it frozen?
+//   spec = true  (head phase behind a programmatic launch): decisions through it-2 are awaited;
+//                 the phase still runs when the test fired at it-1 (see the header comment)
+//   spec = false: decisions through it-1 are awaited; frozen as soon as the test has fired.
+// Every thread of the CTA gets the same answer (0 = nothing to do); contains a __syncthreads().
+__device__ __forceinline__ unsigned long long chain_enter(const GadmmChain& c, int off, bool spec,
+                                                          unsigned long long* s_it) {
+  if (threadIdx.x == 0) {
+    unsigned long long it = *reinterpret_cast<volatile unsigned long long*>(c.sync) +
+                            (unsigned long long)off;
+    bool run = it <= (unsigned long long)c.max_iter;
+    if (run) {
+      const unsigned long long need_dv = spec ? (it >= 2ull ? it - 2ull : 0ull) : it - 1ull;
+      if (c.pdl) wait_flag_ge_gpu(c.sync + 1, need_dv);
+      const unsigned long long hit = *reinterpret_cast<volatile unsigned long long*>(c.ctrl + 1);
+      if (c.ctrl[2] != 0ull && hit != 0ull && hit <= need_dv) run = false;   // converged: frozen
+    }
+    *s_it = run ? it : 0ull;
+  }
+  __syncthreads();
+  return *s_it;
+}
+
+// First launch of a window (ordinary stream order: everything before it has completed).
+__global__ void gadmm_window_begin_kernel(const GadmmChain c) {
+  const unsigned long long it = c.ctrl[0];
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i == 0) {
+    c.sync[0] = it;
+    c.sync[1] = it - 1ull;       // every earlier stop decision is final
+  }
+  if (i < c.Nloc) c.nuflag[i] = it - 1ull;
+}
 
 // NSTAGES = SymvCfg<T>::STAGES: two CTAs per SM (many workers per GPU).  NSTAGES doubled ("deep"):
 // one CTA per SM with twice the bytes in flight, for phases with fewer active CTAs than SMs
 // (one worker per GPU), where a 3-stage ring is latency-bound.
 template <typename T, int NSTAGES>
 __global__ void __launch_bounds__(kSymvThreads, (NSTAGES > SymvCfg<T>::STAGES) ? 1 : 2)
-gadmm_half_iter_kernel(const GadmmChain c, const int color) {
+gadmm_half_iter_kernel(const GadmmChain c, const int color, const int off) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   SymvSmem<T, NSTAGES>& sm = *reinterpret_cast<SymvSmem<T, NSTAGES>*>(smem_raw);
+  __shared__ unsigned long long s_it;
   const int nT = c.dp / kT, npairs = (nT + 1) / 2, nsp = c.nsplit;
   // `order` puts workers with a neighbour on another GPU first: their theta is published early in
   // the phase and the peer's dependent CTAs (scheduled first there, too) do not sit spinning
   const int k = c.order[blockIdx.x / (npairs * nsp)], p = (blockIdx.x / nsp) % npairs,
             part = blockIdx.x % nsp;
-  if (c.color[k] != color) return;
-  const unsigned long long it = c.ctrl[0];
-  if (c.ctrl[2] != 0ull && c.ctrl[1] != 0ull) return;   // converged: freeze the state
-  if (it > (unsigned long long)c.max_iter) return;
-
   // let the next phase's grid start filling SMs as soon as every CTA of this one is resident
   if (c.pdl) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  if (c.color[k] != color) return;
   const int g = c.gid[k], l = c.left[k], r = c.right[k];
-  // heads read the tails' previous iterate, tails read this iteration's heads
-  const unsigned long long need = (color == 0) ? it - 1 : it;
-  const size_t slot_in = (size_t)(need & 1ull) * c.Nglob;
-  if (threadIdx.x == kConsumerWarps * 32) {   // producer lane 0 waits for remote neighbours
-    // With programmatic dependent launch the previous phase may still be running on this GPU,
-    // so local neighbours are awaited through the same version flags as remote ones.
-    if (l >= 0 && (c.pdl || c.owner[l] != c.rank)) wait_flag_ge(c.flags + l, need);
-    if (r >= 0 && (c.pdl || c.owner[r] != c.rank)) wait_flag_ge(c.flags + r, need);
+  size_t slot_in;
+  {
+    const unsigned long long it0 = chain_enter(c, off, c.pdl && color == 0 && off > 0, &s_it);
+    if (it0 == 0ull) return;
+    // heads read the tails' previous iterate, tails read this iteration's heads
+    const unsigned long long need = (color == 0) ? it0 - 1 : it0;
+    slot_in = (size_t)(need & 1ull) * c.Nglob;
+    if (threadIdx.x == kConsumerWarps * 32) {   // producer lane 0 waits for remote neighbours
+      // With programmatic dependent launch the previous phase may still be running on this GPU,
+      // so local neighbours are awaited through the same version flags as remote ones.
+      if (l >= 0 && (c.pdl || c.owner[l] != c.rank)) wait_flag_ge(c.flags + l, need);
+      if (r >= 0 && (c.pdl || c.owner[r] != c.rank)) wait_flag_ge(c.flags + r, need);
+      if (c.pdl) wait_flag_ge_gpu(c.nuflag + k, it0 - 1ull);   // own node dual of iteration it-1
+    }
+    __syncthreads();
   }
-  __syncthreads();
 
   ChainX xf;
   xf.b = c.b + (size_t)k * c.dp;
@@ -117,6 +165,7 @@ gadmm_half_iter_kernel(const GadmmChain c, const int color) {
                                                  xf, rowpart + (size_t)part * c.dp, colpart,
                                                  c.counters + k, npairs * nsp, part, nsp);
   if (!last) return;
+  const unsigned long long it = *reinterpret_cast<volatile unsigned long long*>(&s_it);
   if (c.split_finish) {
     // the partial sums of worker k are complete: hand over to gadmm_finish_kernel (many CTAs)
     if (threadIdx.x == 0) {
@@ -147,7 +196,7 @@ gadmm_half_iter_kernel(const GadmmChain c, const int color) {
   s1 = block_sum(s1, red);
   s2 = block_sum(s2, red);
   if (threadIdx.x == 0) {
-    c.objw[k] = 0.5 * s1 - s2 + c.hyy[k];
+    c.objw[(size_t)(it & 1ull) * c.Nloc + k] = 0.5 * s1 - s2 + c.hyy[k];
     __threadfence_system();
     if (p0 >= 0) st_release_sys(c.flags_peer[p0] + g, it);
     if (p1 >= 0) st_release_sys(c.flags_peer[p1] + g, it);
@@ -163,15 +212,15 @@ gadmm_half_iter_kernel(const GadmmChain c, const int color) {
 // objective pieces and releases the version flags.  Launched with programmatic dependent launch
 // right behind the streaming kernel, so its CTAs fill SM slots as that kernel drains.
 __global__ void __launch_bounds__(64)
-gadmm_finish_kernel(const GadmmChain c, const int color) {
+gadmm_finish_kernel(const GadmmChain c, const int color, const int off) {
   __shared__ double red[8];
   __shared__ unsigned int ticket;
+  __shared__ unsigned long long s_it;
   const int J = blockIdx.x, k = c.order[blockIdx.y], tid = threadIdx.x;
-  if (c.color[k] != color) return;
-  const unsigned long long it = c.ctrl[0];
-  if (c.ctrl[2] != 0ull && c.ctrl[1] != 0ull) return;
-  if (it > (unsigned long long)c.max_iter) return;
   if (c.pdl) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  if (c.color[k] != color) return;
+  const unsigned long long it = chain_enter(c, off, c.pdl && color == 0 && off > 0, &s_it);
+  if (it == 0ull) return;
   const int nT = c.dp / kT;
   const int g = c.gid[k], l = c.left[k], r = c.right[k];
   const unsigned long long need = (color == 0) ? it - 1 : it;
@@ -222,7 +271,7 @@ gadmm_finish_kernel(const GadmmChain c, const int color) {
   __syncthreads();
   if (tid == 0) {
     c.fin_counters[k] = 0u;
-    c.objw[k] = 0.5 * (red[0] + red[2]) - (red[1] + red[3]) + c.hyy[k];
+    c.objw[(size_t)(it & 1ull) * c.Nloc + k] = 0.5 * (red[0] + red[2]) - (red[1] + red[3]) + c.hyy[k];
     __threadfence_system();
     if (p0 >= 0) st_release_sys(c.flags_peer[p0] + g, it);
     if (p1 >= 0) st_release_sys(c.flags_peer[p1] + g, it);
@@ -232,12 +281,13 @@ gadmm_finish_kernel(const GadmmChain c, const int color) {
 
 // --------------------------------------------------------------------- dual update + objective
 __global__ void __launch_bounds__(256)
-gadmm_dual_objective_kernel(const GadmmChain c) {
+gadmm_dual_objective_kernel(const GadmmChain c, const int off) {
   __shared__ double red[32];
   __shared__ unsigned int ticket;
-  const unsigned long long it = c.ctrl[0];
-  if (c.ctrl[2] != 0ull && c.ctrl[1] != 0ull) return;
-  if (it > (unsigned long long)c.max_iter) return;
+  __shared__ unsigned long long s_it;
+  if (c.pdl) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  const unsigned long long it = chain_enter(c, off, false, &s_it);
+  if (it == 0ull) return;
   const int k = c.order[blockIdx.x];
   const int g = c.gid[k], l = c.left[k], r = c.right[k];
   if (threadIdx.x == 0) {
@@ -258,39 +308,56 @@ gadmm_dual_objective_kernel(const GadmmChain c) {
     if (tl) upd = upd - c.rho * (__ldcg(tl + j) - t);
     nu[j] += upd;
   }
-  // ---- last CTA: objective, stop test, clock
+  // ---- nu_k of iteration `it` is in place: worker k's next solve may assemble its RHS
   __threadfence();
   __syncthreads();
-  if (threadIdx.x == 0) ticket = atomicAdd(c.counters + c.Nloc, 1u);
+  if (threadIdx.x == 0) {
+    st_release_gpu(c.nuflag + k, it);
+    // two tickets, used alternately: the kernels of consecutive iterations may overlap
+    ticket = atomicAdd(c.counters + c.Nloc + (int)(it & 1ull), 1u);
+  }
   __syncthreads();
   if (ticket != (unsigned)(c.Nloc - 1)) return;
+  // ---- last CTA: objective, stop test, clock
   __threadfence();
   double part = 0.0;
-  for (int i = threadIdx.x; i < c.Nloc; i += blockDim.x) part += __ldcg(c.objw + i);
+  const double* objw = c.objw + (size_t)(it & 1ull) * c.Nloc;
+  for (int i = threadIdx.x; i < c.Nloc; i += blockDim.x) part += __ldcg(objw + i);
   part = block_sum(part, red);
-  if (threadIdx.x == 0) {
-    c.counters[c.Nloc] = 0u;
-    double total = part;
-    if (c.nranks > 1) {
-      const int ring = (int)(it & 3ull) * c.nranks;
-      for (int q = 0; q < c.nranks; ++q) {
-        double* dst = c.objpart_peer[q] + ring + c.rank;
-        *reinterpret_cast<volatile double*>(dst) = part;
-      }
+  if (threadIdx.x >= 32) return;
+  const int lane = threadIdx.x;
+  if (lane == 0) {
+    c.counters[c.Nloc + (int)(it & 1ull)] = 0u;
+    // decisions are taken in iteration order even when the kernels of two iterations overlap
+    if (c.pdl) wait_flag_ge_gpu(c.sync + 1, it - 1ull);
+  }
+  __syncwarp();
+  double total = part;
+  if (c.nranks > 1) {
+    // all-rank sum: lane q talks to rank q (store + flag out, flag + load in), so the 2*nranks
+    // NVLink round trips overlap instead of queueing behind one thread
+    const int ring = (int)(it & 3ull) * c.nranks;
+    double v = 0.0;
+    if (lane < c.nranks) {
+      *reinterpret_cast<volatile double*>(c.objpart_peer[lane] + ring + c.rank) = part;
       __threadfence_system();
-      for (int q = 0; q < c.nranks; ++q) st_release_sys(c.objflag_peer[q] + ring + c.rank, it);
-      total = 0.0;
-      for (int q = 0; q < c.nranks; ++q) {      // same order on every rank -> identical decision
-        wait_flag_ge(c.objflag + ring + q, it);
-        total += *reinterpret_cast<volatile double*>(c.objpart + ring + q);
-      }
+      st_release_sys(c.objflag_peer[lane] + ring + c.rank, it);
+      wait_flag_ge(c.objflag + ring + lane, it);
+      v = *reinterpret_cast<volatile double*>(c.objpart + ring + lane);
     }
+    total = 0.0;
+    for (int q = 0; q < c.nranks; ++q)          // same order on every rank -> identical decision
+      total += __shfl_sync(0xffffffffu, v, q);
+  }
+  if (lane == 0) {
     const double loss = fabs(total - c.obj0);
     c.obj_hist[it] = total;
     c.loss_hist[it] = loss;
     c.t_hist[it] = globaltimer_ns();
     if (loss < c.acc && c.ctrl[1] == 0ull) c.ctrl[1] = it;
     c.ctrl[0] = it + 1ull;
+    __threadfence();
+    st_release_gpu(c.sync + 1, it);             // the decision of iteration `it` is final
   }
 }
 
@@ -302,31 +369,38 @@ static int configure_half() {
   return 0;
 }
 
+// `dependent`: launch with programmatic stream serialisation (the kernel may start while its
+// predecessor in the stream is still running; it orders itself by flags).
+template <typename... KArgs, typename... Args>
+static cudaError_t launch_k(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem,
+                            cudaStream_t st, bool dependent, Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = dependent ? 1 : 0;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kern, args...);
+}
+
 template <typename T, int NSTAGES>
-static int launch_half_impl(const GadmmChain* c, int color, cudaStream_t st) {
+static int launch_half_impl(const GadmmChain* c, int color, int off, cudaStream_t st) {
   const int smem = (int)sizeof(SymvSmem<T, NSTAGES>);
   const int nT = c->dp / kT, npairs = (nT + 1) / 2;
-  if (c->pdl && color == 1) {
-    // tail phase: programmatic dependent launch behind the head phase (ordering by flags)
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(c->Nloc * npairs * c->nsplit);
-    cfg.blockDim = dim3(kSymvThreads);
-    cfg.dynamicSmemBytes = smem;
-    cfg.stream = st;
-    cudaLaunchAttribute at[1];
-    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    at[0].val.programmaticStreamSerializationAllowed = 1;
-    cfg.attrs = at;
-    cfg.numAttrs = 1;
-    GADMM_CUDA_OK(cudaLaunchKernelEx(&cfg, gadmm_half_iter_kernel<T, NSTAGES>, *c, color));
-  } else {
-    gadmm_half_iter_kernel<T, NSTAGES><<<c->Nloc * npairs * c->nsplit, kSymvThreads, smem, st>>>(*c, color);
-  }
+  // the head phase of a window's first iteration follows gadmm_window_begin_kernel in plain
+  // stream order; every other phase is a dependent launch ordered by flags
+  const bool dependent = c->pdl && !(color == 0 && off == 0);
+  GADMM_CUDA_OK(launch_k(gadmm_half_iter_kernel<T, NSTAGES>, dim3(c->Nloc * npairs * c->nsplit),
+                         dim3(kSymvThreads), smem, st, dependent, *c, color, off));
   return 0;
 }
 
 template <typename T>
-static int launch_half(const GadmmChain* c, int color, cudaStream_t st) {
+static int launch_half(const GadmmChain* c, int color, int off, cudaStream_t st) {
   static PerDeviceState cfg_state;
   int& configured = cfg_state.here();
   constexpr int S1 = SymvCfg<T>::STAGES, S2 = 2 * SymvCfg<T>::STAGES;
@@ -338,22 +412,38 @@ static int launch_half(const GadmmChain* c, int color, cudaStream_t st) {
   const int nT = c->dp / kT, npairs = (nT + 1) / 2;
   // about half of the local workers are active per phase
   const bool deep = c->nsplit == 1 && ((long long)c->Nloc * npairs + 1) / 2 <= 160;
-  if (int e = deep ? launch_half_impl<T, S2>(c, color, st) : launch_half_impl<T, S1>(c, color, st))
+  if (int e = deep ? launch_half_impl<T, S2>(c, color, off, st)
+                   : launch_half_impl<T, S1>(c, color, off, st))
     return e;
+  if (c->split_finish)
+    GADMM_CUDA_OK(launch_k(gadmm_finish_kernel, dim3(nT, c->Nloc), dim3(64), 0, st, c->pdl != 0,
+                           *c, color, off));
+  return 0;
+}
+
+static int chain_check(const GadmmChain* c) {
+  GADMM_REQUIRE(c && c->dp > 0 && c->dp % kT == 0, "chain: dp must be a positive multiple of 64");
+  GADMM_REQUIRE(c->nsplit >= 1 && c->nsplit <= 8, "chain: nsplit must be in [1, 8]");
+  GADMM_REQUIRE(c->Nloc > 0, "chain: every rank must own at least one worker");
+  GADMM_REQUIRE(c->nranks >= 1 && c->nranks <= 32, "chain: at most 32 ranks");
+  GADMM_REQUIRE(c->sync && c->nuflag, "chain: sync / nuflag buffers missing");
+  return 0;
+}
+
+static int window_begin(const GadmmChain* c, cudaStream_t st) {
+  gadmm_window_begin_kernel<<<(c->Nloc + 255) / 256, 256, 0, st>>>(*c);
   GADMM_CUDA_OK(cudaGetLastError());
-  if (c->split_finish) {
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(nT, c->Nloc);
-    cfg.blockDim = dim3(64);
-    cfg.dynamicSmemBytes = 0;
-    cfg.stream = st;
-    cudaLaunchAttribute at[1];
-    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    at[0].val.programmaticStreamSerializationAllowed = c->pdl ? 1 : 0;
-    cfg.attrs = at;
-    cfg.numAttrs = 1;
-    GADMM_CUDA_OK(cudaLaunchKernelEx(&cfg, gadmm_finish_kernel, *c, color));
-  }
+  return 0;
+}
+
+static int half_iter(const GadmmChain* c, int color, int off, cudaStream_t st) {
+  return c->store == GADMM_STORE_F64 ? launch_half<double>(c, color, off, st)
+                                     : launch_half<float>(c, color, off, st);
+}
+
+static int dual_objective(const GadmmChain* c, int off, cudaStream_t st) {
+  GADMM_CUDA_OK(launch_k(gadmm_dual_objective_kernel, dim3(c->Nloc), dim3(256), 0, st,
+                         c->pdl != 0, *c, off));
   return 0;
 }
 
@@ -397,47 +487,37 @@ int gadmm_symv_batched(const void* const* Sptr, const double* x, double* y, int 
   return 0;
 }
 
+/* The two single-launch entry points form a window of ONE iteration: call the head colour, the
+ * tail colour and the dual kernel in that order. */
 int gadmm_chain_half_iter(const GadmmChain* c, int color, void* stream) {
-  GADMM_REQUIRE(c && c->dp > 0 && c->dp % kT == 0, "chain: dp must be a positive multiple of 64");
+  if (int e = chain_check(c)) return e;
   GADMM_REQUIRE(color == 0 || color == 1, "chain: color must be 0 or 1");
-  GADMM_REQUIRE(c->nsplit >= 1 && c->nsplit <= 8, "chain: nsplit must be in [1, 8]");
-  if (c->Nloc <= 0) return 0;
-  return c->store == GADMM_STORE_F64 ? launch_half<double>(c, color, (cudaStream_t)stream)
-                                     : launch_half<float>(c, color, (cudaStream_t)stream);
+  if (color == 0)
+    if (int e = window_begin(c, (cudaStream_t)stream)) return e;
+  return half_iter(c, color, 0, (cudaStream_t)stream);
 }
 
 int gadmm_chain_dual_objective(const GadmmChain* c, void* stream) {
-  GADMM_REQUIRE(c && c->Nloc > 0, "chain: every rank must own at least one worker");
-  if (c->pdl) {
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(c->Nloc);
-    cfg.blockDim = dim3(256);
-    cfg.dynamicSmemBytes = 0;
-    cfg.stream = (cudaStream_t)stream;
-    cudaLaunchAttribute at[1];
-    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    at[0].val.programmaticStreamSerializationAllowed = 1;
-    cfg.attrs = at;
-    cfg.numAttrs = 1;
-    GADMM_CUDA_OK(cudaLaunchKernelEx(&cfg, gadmm_dual_objective_kernel, *c));
-  } else {
-    gadmm_dual_objective_kernel<<<c->Nloc, 256, 0, (cudaStream_t)stream>>>(*c);
-  }
-  GADMM_CUDA_OK(cudaGetLastError());
-  return 0;
+  if (int e = chain_check(c)) return e;
+  return dual_objective(c, 0, (cudaStream_t)stream);
 }
 
 int gadmm_chain_iterate(const GadmmChain* c, int n_iter, void* stream) {
+  if (int e = chain_check(c)) return e;
+  if (n_iter <= 0) return 0;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (int e = window_begin(c, st)) return e;
   for (int i = 0; i < n_iter; ++i) {
     int e;
-    if ((e = gadmm_chain_half_iter(c, 0, stream))) return e;
-    if ((e = gadmm_chain_half_iter(c, 1, stream))) return e;
-    if ((e = gadmm_chain_dual_objective(c, stream))) return e;
+    if ((e = half_iter(c, 0, i, st))) return e;
+    if ((e = half_iter(c, 1, i, st))) return e;
+    if ((e = dual_objective(c, i, st))) return e;
   }
   return 0;
 }
 
-int gadmm_chain_launches_per_iter(void) { return 3; }   /* +2 finisher launches with split_finish */
+int gadmm_chain_launches_per_iter(void) { return 3; }   /* +2 finisher launches with split_finish,
+                                                             +1 per window (window begin) */
 
 int gadmm_chain_configure(void) {
   if (int e = configure_half<double, SymvCfg<double>::STAGES>()) return e;

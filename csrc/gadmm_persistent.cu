@@ -22,15 +22,6 @@ namespace gadmm {
 constexpr int kSyncEvery = 8;
 constexpr int kObjRing = 32;
 
-__device__ __forceinline__ unsigned long long ld_acquire_gpu(const unsigned long long* p) {
-  unsigned long long v;
-  asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ void st_release_gpu(unsigned long long* p, unsigned long long v) {
-  asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
-}
-
 __global__ void __launch_bounds__(256, 1)
 gadmm_persistent_kernel(const GadmmChain c, const int n_iter, double* __restrict__ objring,
                         unsigned int* __restrict__ ringcnt) {
@@ -42,6 +33,8 @@ gadmm_persistent_kernel(const GadmmChain c, const int n_iter, double* __restrict
   double* th = nu + dp;                             // own theta
   double* r = th + dp;
   double* part = r + dp;                            // [4][dp] matvec partials
+  double* hist = part + 4 * dp;                     // [kSyncEvery][2][dp] (theta, nu) of the last
+                                                    // iterations: exact roll-back to the stop iteration
   __shared__ double red[32];
   __shared__ unsigned int s_ticket;
   cg::grid_group grid = cg::this_grid();
@@ -120,6 +113,9 @@ gadmm_persistent_kernel(const GadmmChain c, const int n_iter, double* __restrict
       if (rr >= 0) upd = upd + rho * (th[j] - __ldcg(c.theta + (sout + rr) * dp + j));
       if (l >= 0) upd = upd - rho * (__ldcg(c.theta + (sout + l) * dp + j) - th[j]);
       nu[j] += upd;
+      double* h = hist + (size_t)(it % kSyncEvery) * 2 * dp;
+      h[j] = th[j];
+      h[dp + j] = nu[j];
     }
     // ------------------------------------------------------------------ objective (last arriver)
     const int ring = (int)(it % kObjRing);
@@ -151,12 +147,28 @@ gadmm_persistent_kernel(const GadmmChain c, const int n_iter, double* __restrict
       if (c.ctrl[2] != 0ull && hit <= it) stopped = true;
     }
   }
-  // ---- write the state back so that the general path / checkpointing can continue from here
+  // ---- write the state back so that the general path / checkpointing can continue from here.
+  // The stop is agreed on only every kSyncEvery iterations, so CTAs may have run up to
+  // kSyncEvery-1 iterations past the first crossing `hit`: roll back to the state of iteration
+  // `hit` (the reference breaks there, group_ADMM_closedForm.m:105-108), so that state() / resume
+  // and the general path see exactly what they would have produced.
+  __syncthreads();
+  const unsigned long long hit = *reinterpret_cast<volatile unsigned long long*>(c.ctrl + 3);
+  const bool rolled = stopped && c.ctrl[2] != 0ull && hit != ~0ull && hit + 1ull < it;
+  if (rolled) {
+    const double* h = hist + (size_t)(hit % kSyncEvery) * 2 * dp;
+    const size_t so = (size_t)(hit & 1ull) * c.Nglob;
+    for (int j = tid; j < dp; j += 256) {
+      nu[j] = h[dp + j];
+      c.theta[(so + g) * dp + j] = h[j];
+    }
+    if (tid == 0) c.flags[g] = hit;
+  }
+  __syncthreads();
   for (int j = tid; j < dp; j += 256) c.nu[(size_t)k * dp + j] = nu[j];
   if (k == 0 && tid == 0) {
-    const unsigned long long hit = c.ctrl[3];
     if (c.ctrl[2] != 0ull && hit != ~0ull && hit < it && c.ctrl[1] == 0ull) c.ctrl[1] = hit;
-    c.ctrl[0] = it;
+    c.ctrl[0] = rolled ? hit + 1ull : it;
   }
 }
 
@@ -182,7 +194,8 @@ int gadmm_chain_persistent(const GadmmChain* c, int n_iter, double* objring, uns
                            void* stream) {
   GADMM_REQUIRE(gadmm_chain_persistent_supported(c) == 0, "persistent path: unsupported problem");
   const int dp = c->dp;
-  const size_t smem = ((size_t)dp * dp + 4 * (size_t)dp + 4 * (size_t)dp) * sizeof(double);
+  const size_t smem = ((size_t)dp * dp + 4 * (size_t)dp + 4 * (size_t)dp +
+                       2 * (size_t)kSyncEvery * dp) * sizeof(double);
   GADMM_CUDA_OK(cudaFuncSetAttribute(gadmm_persistent_kernel,
                                      cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   GadmmChain cc = *c;

@@ -94,8 +94,10 @@ class ChainEngine:
             self.nsplit = int(os.environ["GADMM_B200_NSPLIT"])
         self.rowpart = torch.empty((Nloc, self.nsplit, dp), dtype=f64, device=dev)
         self.colpart = torch.empty((Nloc, cpe), dtype=f64, device=dev)
-        self.counters = torch.zeros((Nloc + 1,), dtype=i32, device=dev)
-        self.objw = torch.zeros((Nloc,), dtype=f64, device=dev)
+        self.counters = torch.zeros((Nloc + 2,), dtype=i32, device=dev)
+        self.objw = torch.zeros((2, Nloc), dtype=f64, device=dev)
+        self.sync = torch.zeros((2,), dtype=i64, device=dev)       # window base, decided-through
+        self.nuflag = torch.zeros((Nloc,), dtype=i64, device=dev)
         # parallel finisher (csrc/gadmm_iter.cu: gadmm_finish_kernel) for d >= 512
         self.split_finish = (dp // 64 >= 8) and os.environ.get("GADMM_B200_NO_SPLIT") != "1"
         self.wready = torch.zeros((Nloc,), dtype=i64, device=dev)
@@ -206,6 +208,11 @@ class ChainEngine:
                 mp[k] = self.P[1].data_ptr() + k * pe_bytes
             else:
                 if k not in self.P_end:
+                    if k not in getattr(self, "_G_keep", {}):
+                        raise ValueError(
+                            "a static engine (dynamic=False) only supports chains that start and "
+                            f"end at workers 0 and N-1; worker {int(gid)} is a chain end of this "
+                            "chain -- construct the engine with dynamic=True")
                     A = LA.shifted_inverse(self._G_keep[k], self.d, 1.0 * self.rho)
                     self.P_end[k] = LA.pack_sym(A, self.d, self.store)
                 mp[k] = self.P_end[k].data_ptr()
@@ -271,6 +278,7 @@ class ChainEngine:
         c.split_finish = int(self.split_finish)
         c.nsplit = int(self.nsplit)
         c.order = self.order.data_ptr()
+        c.sync, c.nuflag = self.sync.data_ptr(), self.nuflag.data_ptr()
         c.wready, c.sblk, c.fin_counters = (self.wready.data_ptr(), self.sblk.data_ptr(),
                                             self.fin_counters.data_ptr())
         self._desc = c
@@ -285,7 +293,7 @@ class ChainEngine:
             nv.check(L.gadmm_chain_iterate(C.byref(c), int(n_iter), nv.stream_ptr()))
         else:
             self._capture(n_iter).replay()
-        self.launches += (5 if self.split_finish else 3) * int(n_iter)
+        self.launches += (5 if self.split_finish else 3) * int(n_iter) + 1   # + window begin
 
     def _capture(self, n_iter: int):
         g = self._graphs.get(n_iter)
@@ -380,7 +388,7 @@ class ChainEngine:
                 g.replay()
             else:
                 launch(n)
-            self.launches += (7 if self.split_finish else 5) * n
+            self.launches += (8 if self.split_finish else 6) * n
 
         done, base = 0, 1
         while done < num_iter:
@@ -535,6 +543,36 @@ class ChainEngine:
                 "obj": self.obj_hist[1:it + 1].cpu().numpy().copy(),
                 "loss": self.loss_hist[1:it + 1].cpu().numpy().copy(),
                 "rho": self.rho}
+
+    def reset(self, stop: Optional[bool] = None, acc: Optional[float] = None,
+              obj0: Optional[float] = None):
+        """Back to iteration 0 (zero models and duals) on the same data, inverses and chain, e.g.
+        to measure time-to-accuracy after a throughput run.  Curves and clocks are cleared; the
+        stop test / tolerance / optimum can be changed (captured graphs are dropped with them)."""
+        torch.cuda.synchronize(self.dev)
+        self.dist.barrier()
+        if stop is not None:
+            self.stop = bool(stop)
+        if acc is not None:
+            self.acc = float(acc)
+        if obj0 is not None:
+            self.obj0 = float(obj0)
+        for t in (self.theta, self.flags, self.objpart, self.objflag, self.nu, self.counters,
+                  self.fin_counters, self.wready, self.objw, self.obj_hist, self.loss_hist,
+                  self.t_hist, self.ringcnt, self.nuflag, self.sync):
+            t.zero_()
+        self.ctrl.zero_()
+        self.ctrl[0] = 1
+        self.ctrl[2] = 1 if self.stop else 0
+        self.ctrl[3] = -1
+        self._resume_from = 0
+        self._desc = None
+        self._graphs = {}
+        for name in ("_step_out", "_it_host"):
+            if hasattr(self, name):
+                delattr(self, name)
+        torch.cuda.synchronize(self.dev)
+        self.dist.barrier()
 
     def load_state(self, st):
         """Resume from :meth:`state` (or from an oracle ``return_state`` dict of a node-dual run):

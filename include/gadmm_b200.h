@@ -99,8 +99,8 @@ typedef struct GadmmChain {
   unsigned long long* const* objflag_peer; /* [nranks] */
   double* rowpart;           /* scratch [Nloc][nsplit][dp] */
   double* colpart;           /* scratch [Nloc][dp*dp/128] */
-  unsigned int* counters;    /* [Nloc+1] zero-initialised */
-  double* objw;              /* [Nloc] per-worker objective of the current iteration */
+  unsigned int* counters;    /* [Nloc+2] zero-initialised */
+  double* objw;              /* [2][Nloc] per-worker objective, slot = iteration & 1 */
   unsigned long long* ctrl;  /* [4]: ctrl[0]=iteration about to run (1-based), ctrl[1]=Iter at
                                 which loss<acc first held (0 = not yet), ctrl[2]=stop enabled */
   double* obj_hist;          /* [max_iter+1] objective per iteration (index = iteration) */
@@ -110,8 +110,9 @@ typedef struct GadmmChain {
   double obj0;
   double acc;
   int d, dp, Nglob, Nloc, rank, nranks, store, max_iter;
-  int pdl;                   /* 1: tail and dual kernels use programmatic dependent launch; phase
-                                ordering on one GPU then also goes through the version flags */
+  int pdl;                   /* 1: every launch of a window after its first head phase uses
+                                programmatic dependent launch; all ordering on one GPU then goes
+                                through the version flags, like the ordering between GPUs */
   int split_finish;          /* 1: the column-partial reduction / theta publication of every
                                 worker runs in gadmm_finish_kernel (one 64-thread CTA per 64
                                 entries) instead of in the worker's last streaming CTA */
@@ -123,6 +124,9 @@ typedef struct GadmmChain {
   int reserved;
   const int* order;          /* [Nloc] permutation of the local workers: launch order of their CTAs
                                 (workers with a neighbour on another GPU first) */
+  unsigned long long* sync;  /* [2]: [0] = first iteration of the window being executed, [1] = last
+                                iteration whose stop decision is final (both written on the device) */
+  unsigned long long* nuflag; /* [Nloc] iteration through which nu_k has been updated */
 } GadmmChain;
 
 int gadmm_chain_half_iter(const GadmmChain* c, int color, void* stream);

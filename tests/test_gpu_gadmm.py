@@ -156,3 +156,31 @@ def test_simulated_clock_mode(small_linear):
     step = np.diff(t)
     assert step[0] > 0 and np.allclose(step, step[0], rtol=1e-12)
     assert 1e-6 < step[0] < 1e-2            # two SYMV launches of a 64x64 problem: microseconds
+
+
+@pytest.mark.parametrize("d", [12, 150])
+def test_state_after_early_stop_is_the_state_of_iter(d):
+    """The stop test fires inside a launch window (persistent kernel: between two grid barriers;
+    streaming path: with the next head phase already launched).  The returned state must be the
+    one of iteration ``Iter`` exactly, as if the run had broken there like the reference does
+    (group_ADMM_closedForm.m:105-108): it equals the oracle's state and resumes bit-for-bit."""
+    rng = np.random.default_rng(11)
+    N, s = 7, 20
+    XX = rng.standard_normal((N * s, d))
+    YY = rng.standard_normal(N * s)
+    obj0 = O.opt_sol_closedForm(XX, YY)
+    args = (XX, YY, 2.0, N, d, s)
+    acc = 1e-3
+    o = O.static_group_ADMM_closedForm(*args, 3000, obj0, acc, 10 ** 9, np.ones((1, N - 1)),
+                                       return_state=True)
+    b = g.group_ADMM_closedForm(*args, 3000, obj0, acc, backend="b200", return_state=True)
+    assert b[2] == o[2] and b[2] % 8 != 0 and b[2] % 32 != 0, b[2]
+    st = b[4]
+    assert st["iteration"] == b[2]
+    np.testing.assert_allclose(st["theta"], o[5]["theta"], rtol=1e-9, atol=1e-12)
+    np.testing.assert_allclose(st["dual"], o[5]["dual"], rtol=1e-9, atol=1e-12)
+    # continuing from that state reproduces the uninterrupted run
+    more = b[2] + 37
+    full = g.group_ADMM_closedForm(*args, more, obj0, 0.0, backend="b200")
+    rest = g.group_ADMM_closedForm(*args, more, obj0, 0.0, backend="b200", state=st)
+    np.testing.assert_allclose(rest[0][b[2]:], full[0][b[2]:], rtol=1e-12)
