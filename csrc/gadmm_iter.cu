@@ -287,7 +287,17 @@ gadmm_dual_objective_kernel(const GadmmChain c, const int off) {
   __shared__ unsigned long long s_it;
   if (c.pdl) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   const unsigned long long it = chain_enter(c, off, false, &s_it);
-  if (it == 0ull) return;
+  if (it == 0ull) {
+    // Frozen after the stop test fired: nothing to compute, but later launches of the window
+    // still wait for "the decision of iteration it-1 is final" -- keep that counter moving
+    // (chain_enter has already waited for it-1, so the sequence stays ordered).
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+      const unsigned long long raw = *reinterpret_cast<volatile unsigned long long*>(c.sync) +
+                                     (unsigned long long)off;
+      if (raw <= (unsigned long long)c.max_iter) st_release_gpu(c.sync + 1, raw);
+    }
+    return;
+  }
   const int k = c.order[blockIdx.x];
   const int g = c.gid[k], l = c.left[k], r = c.right[k];
   if (threadIdx.x == 0) {
