@@ -59,6 +59,11 @@ def lib():
     _lib.gadmm_packed_elems.argtypes = [C.c_int]
     _lib.gadmm_symv_scratch_elems.restype = C.c_size_t
     _lib.gadmm_symv_scratch_elems.argtypes = [C.c_int]
+    _lib.gadmm_logistic_xtwx_scratch_elems.restype = C.c_size_t
+    _lib.gadmm_logistic_xtwx_scratch_elems.argtypes = [C.c_int, C.c_int, C.c_int]
+    _lib.gadmm_logi_graph_create.argtypes = [C.c_void_p, C.POINTER(C.c_void_p)]
+    _lib.gadmm_logi_graph_launch.argtypes = [C.c_void_p, C.c_void_p]
+    _lib.gadmm_logi_graph_destroy.argtypes = [C.c_void_p]
     return _lib
 
 
@@ -157,6 +162,27 @@ class GadmmLogistic(C.Structure):
         ("inner_tol", C.c_double), ("obj0", C.c_double), ("acc", C.c_double),
         ("N", C.c_int), ("s", C.c_int), ("d", C.c_int), ("dp", C.c_int), ("max_iter", C.c_int),
         ("max_inner", C.c_int), ("n0", C.c_int), ("nloc", C.c_int),
+    ]
+
+
+class GadmmLogi(C.Structure):
+    """Mirror of ``struct GadmmLogi`` (include/gadmm_b200.h)."""
+    _fields_ = [
+        ("X", _vp), ("y", _vp), ("Dw", _vp), ("table", _vp), ("flags", _vp), ("table_peer", _vp),
+        ("flags_peer", _vp), ("objpart", _vp), ("objflag", _vp), ("objpart_peer", _vp),
+        ("objflag_peer", _vp), ("lam", _vp),
+        ("x", _vp), ("g", _vp), ("p", _vp), ("r", _vp), ("q", _vp), ("hq", _vp), ("xtry", _vp),
+        ("lin", _vp), ("vlast", _vp),
+        ("mu", _vp), ("f", _vp), ("gn", _vp), ("eta", _vp), ("rs", _vp), ("t", _vp), ("slope", _vp),
+        ("losstry", _vp), ("losslast", _vp), ("live", _vp), ("objw", _vp), ("scratch", _vp),
+        ("ctrl", _vp), ("cond", _vp), ("counters", _vp), ("obj_hist", _vp), ("loss_hist", _vp),
+        ("t_hist", _vp),
+        ("rho", C.c_double), ("lam_log", C.c_double), ("obj0", C.c_double), ("acc", C.c_double),
+        ("tol", C.c_double),
+        ("N", C.c_int), ("Nloc", C.c_int), ("g0", C.c_int), ("s", C.c_int), ("d", C.c_int),
+        ("rank", C.c_int), ("nranks", C.c_int), ("store", C.c_int), ("hv_mode", C.c_int),
+        ("max_iter", C.c_int), ("max_newton", C.c_int), ("max_cg", C.c_int), ("max_ls", C.c_int),
+        ("G", C.c_int * 2),
     ]
 
 

@@ -329,6 +329,88 @@ int gadmm_logistic_xtwx(const float* X, const double* y, const double* x, long l
                         double* Dw, double* v, int ldv, double* loss, int N, int s, int d, int G,
                         int hv, int shard_stride, double* scratch, void* stream);
 
+/* Same product with fp64 shards (`store` = GADMM_STORE_F64) or fp32 shards (GADMM_STORE_F32): user
+ * data that is not exactly representable in fp32 stays in double, as the reference computes
+ * (group_ADMM_logistic.m:48-49).  hv = 2 (fp32 multiplies) applies to fp32 shards only. */
+int gadmm_logistic_xtwx_ex(const void* X, int store, const double* y, const double* x,
+                           long long x_stride, double* Dw, double* v, int ldv, double* loss, int N,
+                           int s, int d, int G, int hv, int shard_stride, double* scratch,
+                           void* stream);
+
+/* ---- logistic GADMM with exact local solves, device-resident (K9; group_ADMM_logistic.m:48-55
+ * head solves, :83-86 tail solves, :90-91 dual update, :96-110 objective / stop) ----------------
+ * Every worker's strongly convex sub-problem is solved by a batched Newton-CG whose vector
+ * recurrences, forcing-term test and Armijo line search run in kernels around the one-pass
+ * products above.  The whole run is ONE CUDA graph launch: WHILE nodes (conditional graph nodes,
+ * their conditions set on the device) express iteration / Newton / CG / line-search loops, so
+ * there is no host round trip, no torch op and no NCCL call between the first iteration and the
+ * stop.  Boundary models are stored into the neighbouring GPUs' tables over NVLink followed by a
+ * release flag; the dual update and the all-rank objective sum use the same flags. */
+typedef struct GadmmLogi {
+  const void* X;             /* [Nloc][s][d] shards, fp32 or fp64 (`store`) */
+  const double* y;           /* [Nloc][s] labels +-1 */
+  double* Dw;                /* [Nloc][s] sigma(1-sigma) at the last evaluated point */
+  double* table;             /* symmetric: [N][d] model of every worker (own rows + halo rows) */
+  unsigned long long* flags; /* symmetric: [N] iteration of the model present in `table` */
+  double* const* table_peer; /* [nranks] */
+  unsigned long long* const* flags_peer;
+  double* objpart;           /* symmetric: [4][nranks] objective partials (ring over iterations) */
+  unsigned long long* objflag;
+  double* const* objpart_peer;
+  unsigned long long* const* objflag_peer;
+  double* lam;               /* [Nloc+1][d] edge duals: lam[k] couples global workers g0-1+k, g0+k */
+  /* work vectors of one colour's batched solve, rows = that colour's local workers: [R][d] each */
+  double* x;
+  double* g;
+  double* p;
+  double* r;
+  double* q;
+  double* hq;                /* Hessian product / trial gradient data part (output of the pass) */
+  double* xtry;
+  double* lin;
+  double* vlast;             /* [2][R][d] data part of the gradient at each colour's current models */
+  /* per-row scalars [R] (losslast: [2][R]) */
+  double* mu;
+  double* f;
+  double* gn;
+  double* eta;
+  double* rs;
+  double* t;
+  double* slope;
+  double* losstry;
+  double* losslast;
+  int* live;
+  double* objw;              /* [Nloc] */
+  double* scratch;           /* partial column sums of the pass: xtwx scratch for max(R0,R1) rows */
+  unsigned long long* ctrl;  /* [16]: 0 iteration about to run, 1 Iter at which loss<acc first held,
+                                2 stop enabled, 3 last iteration of this launch, 4 newton count,
+                                5 cg count, 6 line-search count, 8 total Hessian products,
+                                9 total evaluations, 10 total Newton steps */
+  unsigned int* cond;        /* [4] loop conditions as last written (outer, newton, cg, ls) */
+  unsigned int* counters;    /* [8] zero-initialised tickets */
+  double* obj_hist;          /* [max_iter+2] */
+  double* loss_hist;
+  unsigned long long* t_hist;
+  double rho, lam_log, obj0, acc, tol;
+  int N, Nloc, g0, s, d, rank, nranks, store, hv_mode;
+  int max_iter, max_newton, max_cg, max_ls;
+  int G[2];                  /* CTAs per shard of the streaming pass, per colour */
+} GadmmLogi;
+/* 0 when conditional graph nodes work on this driver / device (probe: a WHILE loop counting to n). */
+int gadmm_graph_loops_selftest(int n, void* stream);
+/* Rows of colour c on this rank (R = max over the two colours sizes the work vectors). */
+int gadmm_logi_rows(const GadmmLogi* p, int colour);
+/* Evaluate both colours at the models in `table` (fills vlast / losslast / Dw); call once before
+ * the first run and after the models were changed from outside. */
+int gadmm_logi_prime(const GadmmLogi* p, void* stream);
+/* Build the graph for `p` (pointers and scalars are baked in).  Returns an opaque handle. */
+int gadmm_logi_graph_create(const GadmmLogi* p, void** handle_out);
+int gadmm_logi_graph_launch(void* handle, void* stream);
+int gadmm_logi_graph_destroy(void* handle);
+/* Same iteration driven from the host (one condition read-back per loop test); for debugging and
+ * as the fall-back where conditional nodes are unavailable.  Runs until ctrl[3] or the stop. */
+int gadmm_logi_run_host(const GadmmLogi* p, void* stream);
+
 /* ---- tensor-core Gram (K1 proper): G[n] (+)= X_n' diag(w_n) X_n with tcgen05 kind::tf32 in a
  * 3-product hi/lo split (fp32-grade), TMA-fed, TMEM accumulators, fp64 result.  X: [N][s][d] fp64
  * or fp32; w: optional [N][s] row weights (logistic Hessian X'DX); work: gadmm_gram_tc_workspace_floats
