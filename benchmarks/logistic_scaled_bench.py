@@ -24,6 +24,7 @@ def main():
     ap.add_argument("--rel-acc", type=float, default=0.0, help="stop at gap < rel_acc * obj0 instead of --acc")
     ap.add_argument("--quiet", action="store_true")
     ap.add_argument("--kernel-only", action="store_true")
+    ap.add_argument("--mode", default="auto", choices=["auto", "graph", "host"])
     a = ap.parse_args()
     import torch
     from gadmm_b200.engine.logistic_scaled import ScaledLogisticGadmm
@@ -31,7 +32,7 @@ def main():
     init_process_group()
     D = Dist()
     t0 = time.time()
-    eng = ScaledLogisticGadmm(a.workers, a.d, a.s, a.lam, a.rho, dist=D)
+    eng = ScaledLogisticGadmm(a.workers, a.d, a.s, a.lam, a.rho, dist=D, max_iter=a.iters)
     torch.cuda.synchronize()
     out = {"workers": a.workers, "d": a.d, "s": a.s, "n_gpus": D.world, "rho": a.rho, "lam": a.lam,
            "setup_s": round(time.time() - t0, 3)}
@@ -60,13 +61,14 @@ def main():
         out["optimum_s"] = round(time.time() - t0, 3)
         out["obj0"] = obj0
         acc = a.rel_acc * abs(obj0) if a.rel_acc > 0 else a.acc
-        obj, loss, it, tv = eng.run(a.iters, obj0, acc, verbose=not a.quiet)
+        obj, loss, it, tv = eng.run(a.iters, obj0, acc, verbose=not a.quiet, mode=a.mode)
         st = eng.state()
         out.update({"iterations": int(it), "acc": acc, "reached": bool(loss[-1] < acc), "final_gap": float(loss[-1]),
                     "time_s": float(tv[-1]), "s_per_iter": float(tv[-1] / max(len(tv), 1)),
                     "first_iter_s": float(tv[0]),
                     "s_per_iter_steady": float((tv[-1] - tv[0]) / max(len(tv) - 1, 1)),
-                    "hessvecs": st.get("hessvecs"), "evals": st.get("evals"), "launches": st["launches"]})
+                    "hessvecs": st.get("hessvecs"), "evals": st.get("evals"), "newton_steps": st.get("newton_steps"),
+                    "mode": st.get("mode"), "launches": st["launches"]})
     if D.rank == 0:
         print(json.dumps(out))
     if D.world > 1:

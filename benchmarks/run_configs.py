@@ -119,7 +119,7 @@ def logistic_scaled(D, a):
     import torch
     from gadmm_b200.engine.logistic_scaled import ScaledLogisticGadmm
     t0 = time.time()
-    eng = ScaledLogisticGadmm(a.ls_workers, a.ls_d, a.ls_s, 1e-3, a.ls_rho, dist=D)
+    eng = ScaledLogisticGadmm(a.ls_workers, a.ls_d, a.ls_s, 1e-3, a.ls_rho, dist=D, max_iter=a.ls_iters)
     obj0, _ = eng.solve_optimum()
     torch.cuda.synchronize()
     setup = time.time() - t0

@@ -797,7 +797,7 @@ __global__ void logi_begin_kernel(const GadmmLogi p, const LogiConds lc) {
   const unsigned long long it = p.ctrl[0];
   const bool stopped = p.ctrl[2] != 0ull && p.ctrl[1] != 0ull;
   const bool more = !stopped && it <= p.ctrl[3] && it <= (unsigned long long)p.max_iter;
-  if (it == 1ull) p.t_hist[0] = globaltimer_ns();         // clock origin of the run
+  if (p.t_hist[0] == 0ull) p.t_hist[0] = globaltimer_ns();   // clock origin: the first launch
   logi_set_cond(p, lc, C_OUTER, more ? 1u : 0u);
 }
 

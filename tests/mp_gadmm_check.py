@@ -87,7 +87,7 @@ def main():
     # logistic GADMM, exact local solves by Newton-CG, chain split over the GPUs
     rl = np.random.default_rng(4)
     Nl, sl, dl, laml, rhol = 9, 24, 18, 1e-3, 5.0
-    Xl_ = rl.standard_normal((Nl * sl, dl)).astype(np.float32).astype(np.float64)
+    Xl_ = rl.standard_normal((Nl * sl, dl))          # double data, fp64 shards
     Yl_ = np.where(rl.standard_normal(Nl * sl) > 0, 1.0, -1.0)
     ol = O.opt_sol_logistic(Xl_, Yl_, dl, laml, Nl)
     argl = (Xl_, Yl_, rhol, Nl, dl, sl, 300, ol, laml, 1e-3)

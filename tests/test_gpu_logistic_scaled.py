@@ -57,23 +57,93 @@ def test_xtwx_kernel_matches_fp64(d, s, G, stride, shared):
     assert torch.equal(hv, hv2)
 
 
-def test_scaled_logistic_gadmm_matches_oracle():
+def test_graph_loops_probe():
+    """Conditional (WHILE) graph nodes work on this driver: the engine's device-side loops need them."""
+    from gadmm_b200.engine.logistic_scaled import graph_loops_available
+    from gadmm_b200.ops import native as nv
+    assert nv.lib().gadmm_graph_loops_selftest(7, nv.stream_ptr()) == 0, nv.lib().gadmm_last_error()
+    assert graph_loops_available()
+
+
+@pytest.mark.parametrize("d,s,G,stride", [(8192, 21, 3, 1), (4096, 40, 5, 2), (68, 9, 2, 1), (1024, 64, 8, 1)])
+def test_xtwx_kernel_fp64_shards(d, s, G, stride):
+    """fp64 shards: user data is never rounded to fp32 (group_ADMM_logistic.m computes in double)."""
+    from gadmm_b200.ops import native as nv
+    dev = torch.device("cuda")
+    gen = torch.Generator(device=dev).manual_seed(7 * d + s)
+    Ntot = 4
+    N = (Ntot + stride - 1) // stride
+    X = torch.randn((Ntot, s, d), dtype=torch.float64, device=dev, generator=gen) / np.sqrt(d)
+    y = torch.where(torch.randn((Ntot, s), device=dev, generator=gen) > 0, 1.0, -1.0).double()
+    x = 3.0 * torch.randn((N, d), dtype=torch.float64, device=dev, generator=gen)
+    Dw = torch.zeros((Ntot, s), dtype=torch.float64, device=dev)
+    scratch = torch.empty((int(nv.lib().gadmm_logistic_xtwx_scratch_elems(N, d, G)),),
+                          dtype=torch.float64, device=dev)
+
+    def run(vec, hv):
+        v = torch.empty((N, d), dtype=torch.float64, device=dev)
+        loss = torch.zeros((N,), dtype=torch.float64, device=dev)
+        nv.check(nv.lib().gadmm_logistic_xtwx_ex(
+            nv.ptr(X), nv.STORE_F64, nv.ptr(y), nv.ptr(vec), C.c_longlong(d), nv.ptr(Dw), nv.ptr(v), d,
+            nv.ptr(loss), N, s, d, G, hv, stride, nv.ptr(scratch), nv.stream_ptr()))
+        return v, loss
+
+    Xa, ya = X[::stride], y[::stride]
+    z = torch.einsum("nsd,nd->ns", Xa, x) * ya
+    sig = torch.sigmoid(-z)
+    v, loss = run(x, 0)
+    torch.testing.assert_close(v, -torch.einsum("nsd,ns->nd", Xa, ya * sig), rtol=1e-12, atol=1e-13)
+    torch.testing.assert_close(loss, torch.nn.functional.softplus(-z).sum(1), rtol=1e-12, atol=1e-12)
+    p = torch.randn_like(x)
+    hv, _ = run(p, 1)
+    u = torch.einsum("nsd,nd->ns", Xa, p) * (sig * (1 - sig))
+    torch.testing.assert_close(hv, torch.einsum("nsd,ns->nd", Xa, u), rtol=1e-12, atol=1e-13)
+    hv2, _ = run(p, 2)                       # hv=2 falls back to the exact product on fp64 shards
+    assert torch.equal(hv, hv2)
+
+
+@pytest.mark.parametrize("mode", ["graph", "host"])
+def test_scaled_logistic_gadmm_matches_oracle(mode):
+    """Unrounded double data (fp64 shards are chosen automatically); the device-loop graph and its
+    host-driven twin run the same kernels and give the same curve."""
     from gadmm_b200.engine.logistic_scaled import ScaledLogisticGadmm
+    from gadmm_b200.ops import native as nv
     rng = np.random.default_rng(4)
     N, s, d, lam, rho = 7, 24, 16, 1e-3, 5.0
-    X = rng.standard_normal((N, s, d)).astype(np.float32)
+    X = rng.standard_normal((N, s, d))
     y = np.where(rng.standard_normal((N, s)) > 0, 1.0, -1.0)
-    XX, YY = X.reshape(N * s, d).astype(np.float64), y.reshape(-1)
+    XX, YY = X.reshape(N * s, d), y.reshape(-1)
     obj0 = O.opt_sol_logistic(XX, YY, d, lam, N)
     eng = ScaledLogisticGadmm(N, d, s, lam, rho, data=(X, y))
+    assert eng.store == nv.STORE_F64
     o2, th = eng.solve_optimum()
     assert abs(o2 - obj0) <= 1e-9 * abs(obj0)
     a = O.group_ADMM_logistic(XX, YY, rho, N, d, s, 300, obj0, lam, 1e-3, naive=False, return_state=True)
-    b = eng.run(300, obj0, 1e-3)
+    b = eng.run(300, obj0, 1e-3, mode=mode)
     assert a[2] == b[2] and a[2] < 300
     np.testing.assert_allclose(a[0], b[0], rtol=1e-8)
     np.testing.assert_allclose(a[4]["theta"], eng.state()["theta"], rtol=1e-5, atol=1e-7)
     assert b[3].shape == (b[2],) and np.all(np.diff(b[3]) > 0)
+    assert eng.stats["hessvecs"] > 0 and eng.stats["newton_steps"] > 0
+
+
+def test_scaled_logistic_checkpoint_resume():
+    """state() after 15 iterations -> load_state(): the resumed curve continues the uninterrupted one."""
+    from gadmm_b200.engine.logistic_scaled import ScaledLogisticGadmm
+    rng = np.random.default_rng(14)
+    N, s, d, lam, rho = 6, 20, 12, 1e-3, 3.0
+    X = rng.standard_normal((N, s, d))
+    y = np.where(rng.standard_normal((N, s)) > 0, 1.0, -1.0)
+    full = ScaledLogisticGadmm(N, d, s, lam, rho, data=(X, y)).run(40, 0.0, 0.0)
+    e1 = ScaledLogisticGadmm(N, d, s, lam, rho, data=(X, y))
+    e1.run(15, 0.0, 0.0)
+    st = e1.state()
+    assert st["iteration"] == 15
+    e2 = ScaledLogisticGadmm(N, d, s, lam, rho, data=(X, y))
+    e2.load_state(st)
+    rest = e2.run(40, 0.0, 0.0)
+    assert len(rest[0]) == 40
+    np.testing.assert_allclose(rest[0], full[0], rtol=1e-10)
 
 
 def test_scaled_logistic_synthetic_converges():
@@ -88,7 +158,7 @@ def test_api_routes_to_cg_solver():
     import gadmm_b200 as g
     rng = np.random.default_rng(9)
     N, s, d, lam, rho = 5, 20, 10, 1e-3, 5.0            # d % 4 != 0: zero-padded internally
-    XX = rng.standard_normal((N * s, d)).astype(np.float32).astype(np.float64)
+    XX = rng.standard_normal((N * s, d))              # double data: nothing is rounded to fp32
     YY = np.where(rng.standard_normal(N * s) > 0, 1.0, -1.0)
     obj0 = O.opt_sol_logistic(XX, YY, d, lam, N)
     args = (XX, YY, rho, N, d, s, 300, obj0, lam, 1e-3)

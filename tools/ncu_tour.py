@@ -21,6 +21,7 @@ def main():
     x = torch.randn((148, 8192), dtype=torch.float64, device=eng.dev)
     for mode in (0, 1, 2):                       # gradient / Hessian product fp64 / fp32 multiplies
         eng._xtwx(x, 0, 148, 2, mode)
+    eng.run(1, 0.0, 0.0)                         # one device-resident GADMM iteration (logi_* kernels)
     del eng, x
     torch.cuda.empty_cache()
     # first-order baselines at 128 workers x d = 2048 (packed Grams 2.1 GB)
