@@ -954,30 +954,43 @@ int gadmm_logi_graph_create(const GadmmLogi* p, void** handle_out) {
   LogiPlans pl;
   if (int e = logi_plans(*p, &pl)) return e;
   LogiGraph* lg = new LogiGraph();
+  const char* stage = "cudaGraphCreate";
   cudaError_t err = cudaGraphCreate(&lg->graph, 0);
-  LogiConds lc = {};
-  for (int i = 0; i < 4 && err == cudaSuccess; ++i)
-    err = cudaGraphConditionalHandleCreate(&lc.h[i], lg->graph, 0, 0);
+  // one handle per WHILE node: the iteration loop, and (Newton, CG, line search) per colour
+  LogiConds lc[2] = {};
+  cudaGraphConditionalHandle outer = 0;
   if (err == cudaSuccess) {
+    stage = "cudaGraphConditionalHandleCreate";
+    err = cudaGraphConditionalHandleCreate(&outer, lg->graph, 0, 0);
+  }
+  for (int c = 0; c < 2 && err == cudaSuccess; ++c) {
+    lc[c].h[C_OUTER] = outer;
+    if (logi_rows(*p, c) == 0) continue;
+    for (int i = 1; i < 4 && err == cudaSuccess; ++i)
+      err = cudaGraphConditionalHandleCreate(&lc[c].h[i], lg->graph, 0, 0);
+  }
+  if (err == cudaSuccess) {
+    stage = "adding nodes";
     Sink root;
     root.graph = lg->graph;
-    root.launch(logi_begin_kernel, dim3(1), dim3(1), 0, *p, lc);
+    root.launch(logi_begin_kernel, dim3(1), dim3(1), 0, *p, lc[0]);
     Sink body;
-    root.loop(lc.h[C_OUTER], &body);
+    root.loop(outer, &body);
     if (root.err == cudaSuccess) {
-      graph_half(body, *p, pl, lc, 0);
-      graph_half(body, *p, pl, lc, 1);
-      body.launch(logi_dual_obj_kernel, dim3(p->Nloc + 1), dim3(LG_THREADS), 0, *p, lc);
+      graph_half(body, *p, pl, lc[0], 0);
+      graph_half(body, *p, pl, lc[1], 1);
+      body.launch(logi_dual_obj_kernel, dim3(p->Nloc + 1), dim3(LG_THREADS), 0, *p, lc[0]);
       if (body.err != cudaSuccess) root.err = body.err;
     }
     err = root.err;
   }
+  if (err == cudaSuccess) stage = "cudaGraphInstantiate";
   if (err == cudaSuccess) err = cudaGraphInstantiate(&lg->exec, lg->graph, 0);
   if (err != cudaSuccess) {
     if (lg->graph) cudaGraphDestroy(lg->graph);
     delete lg;
     cudaGetLastError();
-    return set_error((int)err, "logi: building the conditional graph failed: %s",
+    return set_error((int)err, "logi: building the conditional graph failed in %s: %s", stage,
                      cudaGetErrorString(err));
   }
   *handle_out = lg;
