@@ -540,7 +540,11 @@ logi_cg_init_kernel(const GadmmLogi p, const LogiConds lc) {
   if (tid == 0) {
     const double gn = p.gn[n];
     p.rs[n] = rs;
-    p.eta[n] = fmin(sqrt(gn), 0.1) * gn;         // forcing term min(0.1, sqrt|g|) |g|
+    // Forcing term min(1e-2, |g|) |g|.  The local Hessians are mu I plus a small data part, so a
+    // CG step shrinks the residual by ~50x: a tight forcing term costs one or two more Hessian
+    // products per Newton step and saves whole Newton steps (each of which needs at least one
+    // gradient pass, the more expensive of the two passes).
+    p.eta[n] = fmin(gn, 1e-2) * gn;
     if (n == 0) {
       p.ctrl[5] = 0ull;
       logi_set_cond(p, lc, C_CG, 1u);            // the Newton loop runs only with a live row
@@ -635,7 +639,8 @@ logi_ls_step_kernel(const GadmmLogi p, const LogiConds lc) {
   const double f_try = p.losstry[n] + 0.5 * mu * s_xx + s_lx;
   const double f = p.f[n], t = p.t[n];
   // a predicted decrease below the rounding noise of f cannot be tested: accept it
-  const double noise = 64.0 * 2.220446049250313e-16 * fmax(fabs(f), 1.0);
+  // (f is a sum of s log terms over d-long dot products: ~256 ulp of accumulated rounding)
+  const double noise = 256.0 * 2.220446049250313e-16 * fmax(fabs(f), 1.0);
   const bool capped = p.ctrl[6] + 1ull >= (unsigned long long)p.max_ls;
   const bool bad = p.live[n] && t > 1e-9 && (f_try > f - 1e-4 * t * p.slope[n] + noise) && !capped;
   if (bad) {
