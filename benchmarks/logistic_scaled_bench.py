@@ -69,6 +69,14 @@ def main():
                     "s_per_iter_steady": float((tv[-1] - tv[0]) / max(len(tv) - 1, 1)),
                     "hessvecs": st.get("hessvecs"), "evals": st.get("evals"), "newton_steps": st.get("newton_steps"),
                     "mode": st.get("mode"), "launches": st["launches"]})
+        per_rank = [None] * D.world
+        mine = {"rank": D.rank, "hessvecs": st.get("hessvecs"), "evals": st.get("evals"),
+                "newton_steps": st.get("newton_steps"), "wait_ms": st.get("wait_ms")}
+        if D.world > 1:
+            torch.distributed.all_gather_object(per_rank, mine)
+        else:
+            per_rank = [mine]
+        out["per_rank"] = per_rank
     if D.rank == 0:
         print(json.dumps(out))
     if D.world > 1:

@@ -476,9 +476,11 @@ logi_setup_kernel(const GadmmLogi p, const LogiConds lc, const int colour) {
   const unsigned long long it = p.ctrl[0];
   const bool hasL = g > 0, hasR = g < p.N - 1;
   const unsigned long long need = colour == 0 ? it - 1ull : it;
-  if (tid == 0 && p.nranks > 1) {
+  if (tid == 0 && p.nranks > 1 && ((hasL && k == 0) || (hasR && k == p.Nloc - 1))) {
+    const unsigned long long t0 = globaltimer_ns();
     if (hasL && k == 0) wait_flag_ge(p.flags + g - 1, need);
     if (hasR && k == p.Nloc - 1) wait_flag_ge(p.flags + g + 1, need);
+    atomicAdd(p.ctrl + 11, globaltimer_ns() - t0);          // time spent waiting for neighbours
   }
   __syncthreads();
   const double* tl = p.table + (size_t)(hasL ? g - 1 : g) * d;
@@ -627,20 +629,27 @@ logi_ls_step_kernel(const GadmmLogi p, const LogiConds lc) {
   __shared__ unsigned int s_ticket;
   const int n = blockIdx.x, tid = threadIdx.x, d = p.d;
   const double mu = p.mu[n];
-  double s_xx = 0.0, s_lx = 0.0;
+  double s_xx = 0.0, s_lx = 0.0, s_alx = 0.0;
   for (int j = tid; j < d; j += LG_THREADS) {
     const size_t o = (size_t)n * d + j;
     const double xv = p.xtry[o];
+    const double lx = p.lin[o] * xv;
     s_xx = fma(xv, xv, s_xx);
-    s_lx = fma(p.lin[o], xv, s_lx);
+    s_lx += lx;
+    s_alx += fabs(lx);
   }
   s_xx = block_sum(s_xx, red);
   s_lx = block_sum(s_lx, red);
+  s_alx = block_sum(s_alx, red);
   const double f_try = p.losstry[n] + 0.5 * mu * s_xx + s_lx;
   const double f = p.f[n], t = p.t[n];
-  // a predicted decrease below the rounding noise of f cannot be tested: accept it
-  // (f is a sum of s log terms over d-long dot products: ~256 ulp of accumulated rounding)
-  const double noise = 256.0 * 2.220446049250313e-16 * fmax(fabs(f), 1.0);
+  // A predicted decrease below the rounding noise of f cannot be tested: accept it.  f is the sum
+  // of three terms that may cancel (loss, quadratic, linear), each accumulated over thousands of
+  // products, so the noise is taken relative to their magnitudes, not to |f|.  Without this,
+  // rows that are converged to rounding level burn line-search trials (a full pass over the
+  // shards each, for every row of the colour) on coin-flip Armijo tests.
+  const double noise = 256.0 * 2.220446049250313e-16 *
+                       (fabs(p.losstry[n]) + 0.5 * mu * s_xx + s_alx + 1.0);
   const bool capped = p.ctrl[6] + 1ull >= (unsigned long long)p.max_ls;
   const bool bad = p.live[n] && t > 1e-9 && (f_try > f - 1e-4 * t * p.slope[n] + noise) && !capped;
   if (bad) {
@@ -738,9 +747,11 @@ logi_dual_obj_kernel(const GadmmLogi p, const LogiConds lc) {
   const unsigned long long it = p.ctrl[0];
   const int gl = p.g0 - 1 + k, gr = p.g0 + k;              // the edge's end points
   const bool edge = gl >= 0 && gr <= p.N - 1;
-  if (tid == 0 && p.nranks > 1 && edge) {
+  if (tid == 0 && p.nranks > 1 && edge && (k == 0 || k == p.Nloc)) {
+    const unsigned long long t0 = globaltimer_ns();
     if (k == 0) wait_flag_ge(p.flags + gl, it);            // left neighbour GPU's last worker
     if (k == p.Nloc) wait_flag_ge(p.flags + gr, it);       // right neighbour GPU's first worker
+    atomicAdd(p.ctrl + 12, globaltimer_ns() - t0);
   }
   __syncthreads();
   double s_xx = 0.0;
@@ -775,11 +786,14 @@ logi_dual_obj_kernel(const GadmmLogi p, const LogiConds lc) {
       *reinterpret_cast<volatile double*>(p.objpart_peer[lane] + ring + p.rank) = part;
       __threadfence_system();
       st_release_sys(p.objflag_peer[lane] + ring + p.rank, it);
+      const unsigned long long t0 = globaltimer_ns();
       wait_flag_ge(p.objflag + ring + lane, it);
       v = *reinterpret_cast<volatile double*>(p.objpart + ring + lane);
+      if (lane != p.rank) atomicMax(p.ctrl + 14, globaltimer_ns() - t0);
     }
     total = 0.0;
     for (int q = 0; q < p.nranks; ++q) total += __shfl_sync(0xffffffffu, v, q);
+    if (lane == 0) { p.ctrl[13] += p.ctrl[14]; p.ctrl[14] = 0ull; }
   }
   if (lane == 0) {
     const double loss = fabs(total - p.obj0);

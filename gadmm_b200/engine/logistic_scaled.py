@@ -380,7 +380,8 @@ class ScaledLogisticGadmm:
         if self.dist.world > 1 and n_out:
             torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
         self.stats = {"hessvecs": int(self.ctrl[8].item()), "evals": int(self.ctrl[9].item()),
-                      "newton_steps": int(self.ctrl[10].item()), "mode": mode}
+                      "newton_steps": int(self.ctrl[10].item()), "mode": mode,
+                      "wait_ms": [round(int(self.ctrl[i].item()) * 1e-6, 3) for i in (11, 12, 13)]}
         if verbose and self.dist.rank == 0:
             for i in range(n_out):
                 print(f"  iter {1 + i}: obj {obj[i]:.9e} gap {loss[i]:.3e} t {float(t[i]):.3f}s",

@@ -385,7 +385,9 @@ typedef struct GadmmLogi {
   unsigned long long* ctrl;  /* [16]: 0 iteration about to run, 1 Iter at which loss<acc first held,
                                 2 stop enabled, 3 last iteration of this launch, 4 newton count,
                                 5 cg count, 6 line-search count, 8 total Hessian products,
-                                9 total evaluations, 10 total Newton steps */
+                                9 total evaluations, 10 total Newton steps, 11 / 12 / 13 ns spent
+                                waiting for neighbour models (solves / dual step) and for the
+                                other ranks' objective partials */
   unsigned int* cond;        /* [4] loop conditions as last written (outer, newton, cg, ls) */
   unsigned int* counters;    /* [8] zero-initialised tickets */
   double* obj_hist;          /* [max_iter+2] */
