@@ -380,11 +380,13 @@ static int xtwx_configure() {
 // One product v[n] = X_n' w(X_n x_n), n = 0..N-1, into `sink` (two kernels).
 static void emit_xtwx(Sink& k, const XtwxPlan& pl, const void* X, const double* y, const double* x,
                       long long x_stride, double* Dw, double* v, int ldv, double* loss, int N,
-                      int s, int d, int G, int hv, int shard_stride, double* scratch) {
+                      int s, int d, int G, int hv, int shard_stride, double* scratch,
+                      bool reduce = true) {
   double* part = scratch;
   double* losspart = scratch + (size_t)N * G * d;
   k.launch(pl.fn, dim3(G, N), dim3(LS_THREADS), pl.smem, X, y, x, x_stride, Dw, part, losspart, s,
            d, hv, shard_stride);
+  if (!reduce) return;                 // the consumer kernel adds the G partial sums itself
   k.launch(logistic_reduce_kernel, dim3((d + 255) / 256, N), dim3(256), 0, (const double*)part,
            (const double*)losspart, v, loss, G, d, ldv, hv);
 }
@@ -410,7 +412,7 @@ static int xtwx_entry(const void* X, int store, const double* y, const double* x
 // per-row scalars live in global memory; "any row ..." decisions are taken by the last CTA
 // (atomic ticket) which also sets the WHILE condition of the enclosing graph loop.
 // =============================================================================================
-constexpr int LG_THREADS = 256;
+constexpr int LG_THREADS = 1024;  // one CTA per row: wide CTAs keep the per-thread chains short when a GPU holds few rows
 enum { C_OUTER = 0, C_NEWTON = 1, C_CG = 2, C_LS = 3 };
 
 struct LogiConds {                 // conditional handles of the four loops (0 = host-driven mode)
@@ -459,6 +461,32 @@ __device__ __forceinline__ bool logi_last_cta(const GadmmLogi& p, int slot, bool
     }
   }
   return last;
+}
+
+// Start of the CG solve of H p = g for row n (zero start; a masked row keeps r = q = 0 and therefore
+// p = 0), and the trial point / slope that go with p = 0.  Called by the kernels that produce g.
+__device__ __forceinline__ void logi_cg_start(const GadmmLogi& p, int n, bool live, double s_gg) {
+  const int tid = threadIdx.x, d = p.d;
+  const double livef = live ? 1.0 : 0.0;
+  for (int j = tid; j < d; j += LG_THREADS) {
+    const size_t o = (size_t)n * d + j;
+    const double rv = p.g[o] * livef;
+    p.p[o] = 0.0;
+    p.r[o] = rv;
+    p.q[o] = rv;
+    p.xtry[o] = p.x[o];
+  }
+  if (tid == 0) {
+    const double gn = sqrt(s_gg);
+    p.rs[n] = s_gg * livef;
+    // Forcing term min(1e-2, |g|) |g|.  The local Hessians are mu I plus a small data part, so a
+    // CG step shrinks the residual by ~50x: a tight forcing term costs one or two more Hessian
+    // products per Newton step and saves whole Newton steps (each of which needs at least one
+    // gradient pass, the more expensive of the two passes).
+    p.eta[n] = fmin(gn, 1e-2) * gn;
+    p.t[n] = livef;
+    p.slope[n] = 0.0;
+  }
 }
 
 // ---- start of a colour's half-iteration: neighbours' models -> linear term, warm start, and the
@@ -516,107 +544,72 @@ logi_setup_kernel(const GadmmLogi p, const LogiConds lc, const int colour) {
     p.gn[n] = gn;
     p.live[n] = live ? 1 : 0;
   }
+  __syncthreads();                               // g, x of this row are in place
+  logi_cg_start(p, n, live, s_gg);
   bool any;
   if (logi_last_cta(p, 0, live, &s_ticket, &any) && tid == 0) {
     p.ctrl[4] = 0ull;
+    p.ctrl[5] = 0ull;
+    logi_set_cond(p, lc, C_CG, 1u);              // a Newton step starts with at least one CG step
     logi_set_cond(p, lc, C_NEWTON, any ? 1u : 0u);
   }
 }
 
-// ---- CG start for the Newton system H p = g (zero start, masked rows stay zero)
+// ---- one CG step.  The pass left G partial column sums per row in `scratch`; they are added here
+// in a fixed order (deterministic) together with the regulariser mu q.  The step also keeps the
+// line search's starting point up to date (xtry = x - p for live rows, slope = g'p), so that the
+// line search can start as soon as the CG loop ends, whenever that is.
 __global__ void __launch_bounds__(LG_THREADS)
-logi_cg_init_kernel(const GadmmLogi p, const LogiConds lc) {
-  __shared__ double red[32];
-  const int n = blockIdx.x, tid = threadIdx.x, d = p.d;
-  const double livef = p.live[n] ? 1.0 : 0.0;
-  double rs = 0.0;
-  for (int j = tid; j < d; j += LG_THREADS) {
-    const size_t o = (size_t)n * d + j;
-    const double rv = p.g[o] * livef;
-    p.p[o] = 0.0;
-    p.r[o] = rv;
-    p.q[o] = rv;
-    rs = fma(rv, rv, rs);
-  }
-  rs = block_sum(rs, red);
-  if (tid == 0) {
-    const double gn = p.gn[n];
-    p.rs[n] = rs;
-    // Forcing term min(1e-2, |g|) |g|.  The local Hessians are mu I plus a small data part, so a
-    // CG step shrinks the residual by ~50x: a tight forcing term costs one or two more Hessian
-    // products per Newton step and saves whole Newton steps (each of which needs at least one
-    // gradient pass, the more expensive of the two passes).
-    p.eta[n] = fmin(gn, 1e-2) * gn;
-    if (n == 0) {
-      p.ctrl[5] = 0ull;
-      logi_set_cond(p, lc, C_CG, 1u);            // the Newton loop runs only with a live row
-    }
-  }
-}
-
-// ---- one CG step; hq holds X'DXq from the pass, the regulariser mu q is added here
-__global__ void __launch_bounds__(LG_THREADS)
-logi_cg_step_kernel(const GadmmLogi p, const LogiConds lc) {
+logi_cg_step_kernel(const GadmmLogi p, const LogiConds lc, const int colour) {
   __shared__ double red[32];
   __shared__ unsigned int s_ticket;
   const int n = blockIdx.x, tid = threadIdx.x, d = p.d;
-  const double mu = p.mu[n], rs = p.rs[n];
+  const int G = p.G[colour] > 0 ? p.G[colour] : 1;
+  const double* part = p.scratch + (size_t)n * G * d;
+  const double mu = p.mu[n], rs = p.rs[n], t = p.t[n];
   double qhq = 0.0;
   for (int j = tid; j < d; j += LG_THREADS) {
     const size_t o = (size_t)n * d + j;
     const double qv = p.q[o];
-    const double hv = p.hq[o] + mu * qv;
+    double hv = 0.0;
+    for (int g = 0; g < G; ++g) hv += __ldcg(part + (size_t)g * d + j);
+    hv = fma(mu, qv, hv);
     p.hq[o] = hv;
     qhq = fma(qv, hv, qhq);
   }
   qhq = block_sum(qhq, red);
   const double alpha = qhq > 0.0 ? rs / qhq : 0.0;
-  double rs_new = 0.0;
+  double rs_new = 0.0, slope = 0.0;
   for (int j = tid; j < d; j += LG_THREADS) {
     const size_t o = (size_t)n * d + j;
-    p.p[o] = fma(alpha, p.q[o], p.p[o]);
+    const double pv = fma(alpha, p.q[o], p.p[o]);
+    p.p[o] = pv;
     const double rv = fma(-alpha, p.hq[o], p.r[o]);
     p.r[o] = rv;
     rs_new = fma(rv, rv, rs_new);
+    slope = fma(p.g[o], pv, slope);
+    p.xtry[o] = fma(-t, pv, p.x[o]);
   }
   rs_new = block_sum(rs_new, red);
+  slope = block_sum(slope, red);
   const double beta = rs > 0.0 ? rs_new / rs : 0.0;
   for (int j = tid; j < d; j += LG_THREADS) {
     const size_t o = (size_t)n * d + j;
     p.q[o] = fma(beta, p.q[o], p.r[o]);
   }
-  if (tid == 0) p.rs[n] = rs_new;
+  if (tid == 0) {
+    p.rs[n] = rs_new;
+    p.slope[n] = slope;
+  }
   const bool more = sqrt(rs_new) > p.eta[n];
   bool any;
   if (logi_last_cta(p, 2, more, &s_ticket, &any) && tid == 0) {
     const unsigned long long c = p.ctrl[5] + 1ull;
     p.ctrl[5] = c;
+    p.ctrl[6] = 0ull;
     p.ctrl[8] += 1ull;
+    logi_set_cond(p, lc, C_LS, 1u);              // the line search evaluates at least once
     logi_set_cond(p, lc, C_CG, (any && c < (unsigned long long)p.max_cg) ? 1u : 0u);
-  }
-}
-
-// ---- line search start: full Newton step for live rows, t = 0 for the others
-__global__ void __launch_bounds__(LG_THREADS)
-logi_ls_init_kernel(const GadmmLogi p, const LogiConds lc) {
-  __shared__ double red[32];
-  const int n = blockIdx.x, tid = threadIdx.x, d = p.d;
-  const double t = p.live[n] ? 1.0 : 0.0;
-  double slope = 0.0;
-  for (int j = tid; j < d; j += LG_THREADS) {
-    const size_t o = (size_t)n * d + j;
-    const double pv = p.p[o];
-    slope = fma(p.g[o], pv, slope);
-    p.xtry[o] = fma(-t, pv, p.x[o]);
-  }
-  slope = block_sum(slope, red);
-  if (tid == 0) {
-    p.slope[n] = slope;
-    p.t[n] = t;
-    if (n == 0) {
-      p.ctrl[6] = 0ull;
-      logi_set_cond(p, lc, C_LS, 1u);
-    }
   }
 }
 
@@ -624,15 +617,28 @@ logi_ls_init_kernel(const GadmmLogi p, const LogiConds lc) {
 // halve their step and every row is evaluated again, so that the last evaluation is at the
 // accepted points of ALL rows (its data terms and curvature state are reused afterwards).
 __global__ void __launch_bounds__(LG_THREADS)
-logi_ls_step_kernel(const GadmmLogi p, const LogiConds lc) {
+logi_ls_step_kernel(const GadmmLogi p, const LogiConds lc, const int colour) {
   __shared__ double red[32];
   __shared__ unsigned int s_ticket;
+  __shared__ double s_loss;
   const int n = blockIdx.x, tid = threadIdx.x, d = p.d;
+  const int G = p.G[colour] > 0 ? p.G[colour] : 1;
+  const double* part = p.scratch + (size_t)n * G * d;
   const double mu = p.mu[n];
+  if (tid == 0) {                                // loss of the trial point: G partials, fixed order
+    const double* lp = p.scratch + (size_t)gridDim.x * G * d + (size_t)n * G;
+    double l = 0.0;
+    for (int g = 0; g < G; ++g) l += __ldcg(lp + g);
+    p.losstry[n] = l;
+    s_loss = l;
+  }
   double s_xx = 0.0, s_lx = 0.0, s_alx = 0.0;
   for (int j = tid; j < d; j += LG_THREADS) {
     const size_t o = (size_t)n * d + j;
     const double xv = p.xtry[o];
+    double v = 0.0;                              // data part of the trial gradient
+    for (int g = 0; g < G; ++g) v += __ldcg(part + (size_t)g * d + j);
+    p.hq[o] = v;
     const double lx = p.lin[o] * xv;
     s_xx = fma(xv, xv, s_xx);
     s_lx += lx;
@@ -641,7 +647,8 @@ logi_ls_step_kernel(const GadmmLogi p, const LogiConds lc) {
   s_xx = block_sum(s_xx, red);
   s_lx = block_sum(s_lx, red);
   s_alx = block_sum(s_alx, red);
-  const double f_try = p.losstry[n] + 0.5 * mu * s_xx + s_lx;
+  const double loss_try = s_loss;                // (block_sum's barriers make it visible)
+  const double f_try = loss_try + 0.5 * mu * s_xx + s_lx;
   const double f = p.f[n], t = p.t[n];
   // A predicted decrease below the rounding noise of f cannot be tested: accept it.  f is the sum
   // of three terms that may cancel (loss, quadratic, linear), each accumulated over thousands of
@@ -649,7 +656,7 @@ logi_ls_step_kernel(const GadmmLogi p, const LogiConds lc) {
   // rows that are converged to rounding level burn line-search trials (a full pass over the
   // shards each, for every row of the colour) on coin-flip Armijo tests.
   const double noise = 256.0 * 2.220446049250313e-16 *
-                       (fabs(p.losstry[n]) + 0.5 * mu * s_xx + s_alx + 1.0);
+                       (fabs(loss_try) + 0.5 * mu * s_xx + s_alx + 1.0);
   const bool capped = p.ctrl[6] + 1ull >= (unsigned long long)p.max_ls;
   const bool bad = p.live[n] && t > 1e-9 && (f_try > f - 1e-4 * t * p.slope[n] + noise) && !capped;
   if (bad) {
@@ -700,11 +707,15 @@ logi_newton_next_kernel(const GadmmLogi p, const LogiConds lc, const int colour)
     p.live[n] = live ? 1 : 0;
     p.losslast[(size_t)colour * R + n] = p.losstry[n];
   }
+  __syncthreads();
+  logi_cg_start(p, n, live, s_gg);               // ready for the next Newton step, if there is one
   bool any;
   if (logi_last_cta(p, 0, live, &s_ticket, &any) && tid == 0) {
     const unsigned long long c = p.ctrl[4] + 1ull;
     p.ctrl[4] = c;
+    p.ctrl[5] = 0ull;
     p.ctrl[10] += 1ull;
+    logi_set_cond(p, lc, C_CG, 1u);
     logi_set_cond(p, lc, C_NEWTON, (any && c < (unsigned long long)p.max_newton) ? 1u : 0u);
   }
 }
@@ -861,20 +872,21 @@ static LogiShards logi_shards(const GadmmLogi& p, int colour) {
   return sh;
 }
 
+// reduce = false: the G partial sums stay in p.scratch for the consumer kernel (cg_step / ls_step)
 static void emit_eval(Sink& k, const GadmmLogi& p, const LogiPlans& pl, int colour, const double* x,
-                      long long x_stride, double* v, double* loss) {
+                      long long x_stride, double* v, double* loss, bool reduce) {
   const LogiShards sh = logi_shards(p, colour);
   emit_xtwx(k, pl.grad, sh.X, sh.y, x, x_stride, sh.Dw, v, p.d, loss, sh.rows, p.s, p.d, sh.G, 0, 2,
-            p.scratch);
+            p.scratch, reduce);
 }
 static void emit_hessvec(Sink& k, const GadmmLogi& p, const LogiPlans& pl, int colour) {
   const LogiShards sh = logi_shards(p, colour);
   emit_xtwx(k, pl.hv, sh.X, sh.y, p.q, p.d, sh.Dw, p.hq, p.d, p.losstry, sh.rows, p.s, p.d, sh.G,
-            p.hv_mode == 2 ? 2 : 1, 2, p.scratch);
+            p.hv_mode == 2 ? 2 : 1, 2, p.scratch, false);
 }
 
-// One colour's half-iteration as a graph: setup -> WHILE newton { cg_init -> WHILE cg { X'DXq,
-// cg_step } -> ls_init -> WHILE ls { evaluate(xtry), ls_step } -> newton_next } -> publish
+// One colour's half-iteration as a graph: setup -> WHILE newton { WHILE cg { X'DXq, cg_step } ->
+// WHILE ls { evaluate(xtry), ls_step } -> newton_next } -> publish
 static void graph_half(Sink& k, const GadmmLogi& p, const LogiPlans& pl, const LogiConds& lc,
                        int colour) {
   const int rows = logi_rows(p, colour);
@@ -885,20 +897,18 @@ static void graph_half(Sink& k, const GadmmLogi& p, const LogiPlans& pl, const L
   k.loop(lc.h[C_NEWTON], &nw);
   if (k.err != cudaSuccess) return;
   {
-    nw.launch(logi_cg_init_kernel, grid, block, 0, p, lc);
     Sink cg;
     nw.loop(lc.h[C_CG], &cg);
     if (nw.err == cudaSuccess) {
       emit_hessvec(cg, p, pl, colour);
-      cg.launch(logi_cg_step_kernel, grid, block, 0, p, lc);
+      cg.launch(logi_cg_step_kernel, grid, block, 0, p, lc, colour);
       if (cg.err != cudaSuccess) nw.err = cg.err;
     }
-    nw.launch(logi_ls_init_kernel, grid, block, 0, p, lc);
     Sink ls;
     nw.loop(lc.h[C_LS], &ls);
     if (nw.err == cudaSuccess) {
-      emit_eval(ls, p, pl, colour, p.xtry, p.d, p.hq, p.losstry);
-      ls.launch(logi_ls_step_kernel, grid, block, 0, p, lc);
+      emit_eval(ls, p, pl, colour, p.xtry, p.d, p.hq, p.losstry, false);
+      ls.launch(logi_ls_step_kernel, grid, block, 0, p, lc, colour);
       if (ls.err != cudaSuccess) nw.err = ls.err;
     }
     nw.launch(logi_newton_next_kernel, grid, block, 0, p, lc, colour);
@@ -961,7 +971,7 @@ int gadmm_logi_prime(const GadmmLogi* p, void* stream) {
     if (logi_rows(*p, colour) == 0) continue;
     const int first = logi_first(*p, colour);
     emit_eval(k, *p, pl, colour, p->table + (size_t)(p->g0 + first) * p->d, 2ll * p->d,
-              p->vlast + (size_t)colour * R * p->d, p->losslast + (size_t)colour * R);
+              p->vlast + (size_t)colour * R * p->d, p->losslast + (size_t)colour * R, true);
   }
   GADMM_CUDA_OK(k.err);
   GADMM_CUDA_OK(cudaGetLastError());
@@ -1055,19 +1065,17 @@ int gadmm_logi_run_host(const GadmmLogi* p, void* stream) {
       unsigned int cn = 0;
       if (int e = read_cond(*p, C_NEWTON, st, &cn)) return e;
       while (cn) {
-        k.launch(logi_cg_init_kernel, grid, block, 0, *p, lc);
         unsigned int cc = 1;
         while (cc) {
           emit_hessvec(k, *p, pl, colour);
-          k.launch(logi_cg_step_kernel, grid, block, 0, *p, lc);
+          k.launch(logi_cg_step_kernel, grid, block, 0, *p, lc, colour);
           GADMM_CUDA_OK(k.err);
           if (int e = read_cond(*p, C_CG, st, &cc)) return e;
         }
-        k.launch(logi_ls_init_kernel, grid, block, 0, *p, lc);
         unsigned int cl = 1;
         while (cl) {
-          emit_eval(k, *p, pl, colour, p->xtry, p->d, p->hq, p->losstry);
-          k.launch(logi_ls_step_kernel, grid, block, 0, *p, lc);
+          emit_eval(k, *p, pl, colour, p->xtry, p->d, p->hq, p->losstry, false);
+          k.launch(logi_ls_step_kernel, grid, block, 0, *p, lc, colour);
           GADMM_CUDA_OK(k.err);
           if (int e = read_cond(*p, C_LS, st, &cl)) return e;
         }
