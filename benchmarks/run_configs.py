@@ -145,7 +145,7 @@ def baselines_scaled(D, a):
     t0 = time.time()
     fo, obj0 = build_scaled_first_order(N, d, s)
     alpha = 1.0 / fo.lambda_max(tol=1e-9, max_it=400)
-    Hmax = fo.hmax_per_worker(30)
+    Hmax = fo.hmax_per_worker(30, tol=None)
     setup = time.time() - t0
     thr = 10.0 / (alpha ** 2 * N ** 2) / 10
     runs = (("GD", lambda: fo.run_shared(nv.FO_GD, alpha, 0.0, Hmax, T, obj0, None)),

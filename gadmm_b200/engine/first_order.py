@@ -55,6 +55,11 @@ class FirstOrder:
         else:
             self.wbuf = torch.empty((N, s), dtype=torch.float64, device=self.dev)
         del G
+        self._alloc_tables()
+
+    def _alloc_tables(self):
+        """Gradient table (and, across GPUs, the chain-halo tables in symmetric memory)."""
+        N = self.N
         self._own_sym = None
         if self.dist is not None:
             # chain-halo tables (DGD / dual averaging across GPUs): Ytab | Ztab[2] | rowflag[2] |
@@ -75,11 +80,15 @@ class FirstOrder:
         self.launches = 0
 
     @classmethod
-    def from_parts(cls, P, b, hyy, Gsum, N, d, device=None):
+    def from_parts(cls, P, b, hyy, Gsum, N, d, device=None, dist=None, gid0=0, Nglob=None):
         """Least-squares engine from device-resident pieces (packed Grams ``P`` (N, packed), ``b``
-        (N, dp), ``0.5 y'y`` (N,), ``sum_n G_n`` (dp, dp)): the scaled configs never hold X."""
+        (N, dp), ``0.5 y'y`` (N,), ``sum_n G_n`` (dp, dp) over ALL workers): the scaled configs
+        never hold X.  With ``dist`` (world > 1) the pieces are this rank's workers
+        ``gid0 .. gid0+N-1`` of ``Nglob``."""
         self = cls.__new__(cls)
-        self.dist, self.Nglob, self.gid0, self._own_sym = None, int(N), 0, None
+        self.dist = dist if (dist is not None and dist.world > 1) else None
+        self.Nglob = int(Nglob if Nglob is not None else N)
+        self.gid0 = int(gid0) if self.dist is not None else 0
         self.dev = device or P.device
         self.N, self.d, self.s, self.logistic, self.lam = int(N), int(d), 0, False, 0.0
         self.dp = nv.padded(self.d)
@@ -89,14 +98,15 @@ class FirstOrder:
         self.scratch = torch.empty((N, nv.symv_scratch_elems(self.dp)), dtype=torch.float64,
                                    device=self.dev)
         self.cnt = torch.zeros((N,), dtype=torch.int32, device=self.dev)
-        self.Y = torch.zeros((N, self.dp), dtype=torch.float64, device=self.dev)
-        self.fw = torch.zeros((N,), dtype=torch.float64, device=self.dev)
-        self.launches = 0
+        self._alloc_tables()
         return self
 
-    def hmax_per_worker(self, iters: int = 60) -> np.ndarray:
+    def hmax_per_worker(self, iters: int = 60, tol: float = 1e-10, max_it: int = 20000) -> np.ndarray:
         """``Hmax(i) = max(eig(X{i}'*X{i}))`` for every worker at once: batched power iteration on
-        the packed Grams (LinearRegression_Synthetic.m:33)."""
+        the packed Grams (LinearRegression_Synthetic.m:33).  At least ``iters`` iterations, then
+        until every worker's Rayleigh quotient has settled to ``tol`` (relative change over 8
+        iterations; clustered spectra need far more than a fixed count), at most ``max_it``.
+        ``Hmax`` feeds the LAG-PS trigger and the R-IAG sampling (GD_DGD_LAG.m:8,218,357)."""
         mv = LA.BatchedSymv(self.P, self.dp)
         g = torch.Generator(device=self.dev)
         g.manual_seed(1)
@@ -104,10 +114,16 @@ class FirstOrder:
         v[:, :self.d] = torch.rand((self.N, self.d), dtype=torch.float64, device=self.dev, generator=g) + 0.5
         v /= v.norm(dim=1, keepdim=True)
         w = torch.empty_like(v)
-        for _ in range(iters):
+        lam = prev = None
+        for i in range(max(int(iters), 1) if tol is None else int(max_it)):
             mv(v, out=w)
             lam = (v * w).sum(1)
-            v = w / w.norm(dim=1, keepdim=True)
+            v = w / torch.clamp(w.norm(dim=1, keepdim=True), min=1e-300)
+            if tol is not None and i + 1 >= iters and (i + 1) % 8 == 0:
+                if prev is not None and bool(((lam - prev).abs() <= tol * lam.abs()).all().item()):
+                    break
+                prev = lam.clone()
+        self.hmax_iterations = i + 1
         return lam.cpu().numpy()
 
     # ---------------------------------------------------------------------------------------

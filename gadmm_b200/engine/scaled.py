@@ -148,3 +148,59 @@ def build_scaled_first_order(N: int, d: int, s: int, seed: int = 0, noise: float
     bs = b.sum(0)
     obj0 = 0.5 * float(th @ (Gsum @ th)) - float(bs @ th) + float(hyy.sum())
     return FirstOrder.from_parts(P, b, hyy, Gsum, N, d, dev), obj0
+
+
+# ------------------------------------------------------------------------------------------
+# One data set for every algorithm and every partition (BASELINE.json config 2: GADMM vs star ADMM
+# vs GD / DGD / LAG / dual averaging on the same 1024 x 4096 problem): worker g's shard comes from
+# Philox stream g, so chain segments, star worker ranges and parameter-server ranges over any
+# number of GPUs all see the same X_g, y_g.
+def scaled_theta_true(d: int, seed: int, dev):
+    from ..ops.topology import philox_normal
+    return philox_normal((d,), seed * 7919 + 17, 0xFFFF, 0.0, 1.0, device=dev)
+
+
+def worker_grams(gids, d: int, s: int, dp: int, seed: int = 0, noise: float = 0.1, dev=None,
+                 batch: int = 16):
+    """Yield ``(k0, G, b, hyy)`` for consecutive batches of the workers ``gids`` (global ids):
+    ``X_g = Z_g / sqrt(s)`` (fp32 draws widened to fp64), ``y_g = X_g theta* + noise``."""
+    from ..ops.topology import philox_normal
+    dev = dev or torch.device("cuda", torch.cuda.current_device())
+    th = scaled_theta_true(d, seed, dev)
+    gids = [int(g) for g in gids]
+    sd = 1.0 / np.sqrt(s)
+    X32 = torch.empty((s, d), dtype=torch.float32, device=dev)
+    for k0 in range(0, len(gids), batch):
+        ids = gids[k0:k0 + batch]
+        X = torch.empty((len(ids), s, d), dtype=torch.float64, device=dev)
+        y = torch.empty((len(ids), s), dtype=torch.float64, device=dev)
+        for i, g in enumerate(ids):
+            philox_normal(None, seed, g, 0.0, sd, out=X32)
+            X[i].copy_(X32)
+            y[i] = X[i] @ th + philox_normal((s,), seed + 1, g, 0.0, noise, device=dev)
+        G, b, hyy = LA.gram(X, y, dp)
+        del X
+        yield k0, G, b, hyy
+
+
+def scaled_optimum(N: int, d: int, s: int, dp: int, dist, seed: int = 0, noise: float = 0.1,
+                   batch: int = 16):
+    """``(obj0, Gsum, bsum, hsum)`` of the data set above: summed Gram over all workers (each rank
+    sums its share, one all-reduce), normal equations in fp64 (K12)."""
+    from ..parallel.runtime import partition
+    dev = dist.device
+    own = np.nonzero(partition(N, dist.world) == dist.rank)[0]
+    Gsum = torch.zeros((dp, dp), dtype=torch.float64, device=dev)
+    bsum = torch.zeros((dp,), dtype=torch.float64, device=dev)
+    hsum = torch.zeros((), dtype=torch.float64, device=dev)
+    for _, G, b, hyy in worker_grams(own, d, s, dp, seed, noise, dev, batch):
+        Gsum += G.sum(0)
+        bsum += b.sum(0)
+        hsum += hyy.sum()
+    dist.all_reduce_sum_(Gsum)
+    dist.all_reduce_sum_(bsum)
+    dist.all_reduce_sum_(hsum)
+    A = LA.shifted_inverse(Gsum.unsqueeze(0).clone(), d, 0.0)
+    th = LA.BatchedSymv(LA.pack_sym(A, d), dp)(bsum.unsqueeze(0))[0]
+    obj0 = 0.5 * float(th @ (Gsum @ th)) - float(bsum @ th) + float(hsum)
+    return obj0, Gsum, bsum, hsum

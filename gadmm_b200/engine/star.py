@@ -33,20 +33,16 @@ class StarEngine:
         Nw = self.Nw = len(self.gids)
         if Nw == 0:
             raise ValueError("every rank must own at least one worker")
-        XX = np.asarray(XX, dtype=np.float64)
-        YY = np.asarray(YY, dtype=np.float64).reshape(-1)
         dp, f64 = self.dp, torch.float64
-        g0, g1 = int(self.gids[0]), int(self.gids[-1]) + 1
-        X = torch.from_numpy(XX[g0 * s:g1 * s, :d].reshape(Nw, s, d)).to(dev)
-        y = torch.from_numpy(YY[g0 * s:g1 * s].reshape(Nw, s)).to(dev)
-        G, self.b, self.hyy = LA.gram(X, y, dp)
-        self.P = LA.pack_sym(LA.shifted_inverse(G, d, rho), d, self.store)
+        pe = nv.packed_elems(dp)
+        pdt = f64 if self.store == nv.STORE_F64 else torch.float32
+        self.P = torch.empty((Nw, pe), dtype=pdt, device=dev)
+        self.Ps = torch.empty((1, pe), dtype=pdt, device=dev)
+        self.b = torch.zeros((Nw, dp), dtype=f64, device=dev)
+        self.hyy = torch.zeros((Nw,), dtype=f64, device=dev)
+        self.bs = torch.zeros((dp,), dtype=f64, device=dev)
+        self.hyy_s = 0.0
         self.Mptr = LA.ptr_table(self.P)
-        Xs = torch.from_numpy(XX[(N - 1) * s:N * s, :d].reshape(1, s, d)).to(dev)
-        ys = torch.from_numpy(YY[(N - 1) * s:N * s].reshape(1, s)).to(dev)
-        Gs, bs, hs = LA.gram(Xs, ys, dp)
-        self.Ps = LA.pack_sym(LA.shifted_inverse(Gs, d, (N - 1) * rho), d, self.store)
-        self.bs, self.hyy_s = bs[0].contiguous(), float(hs[0].item())
         self.lam = torch.zeros((Nw, dp), dtype=f64, device=dev)
         self.theta = torch.zeros((Nw, dp), dtype=f64, device=dev)
         self.U = torch.zeros((Nw, dp), dtype=f64, device=dev)
@@ -75,9 +71,15 @@ class StarEngine:
         if nvls is True and W > 1 and not mc:
             raise RuntimeError("NVLS multicast is not available for this process group")
         cpe = max(1, (dp // 64) * (dp // 64 - 1) // 2 * 64)
-        self.rowpart = torch.empty((Nw + 1, dp), dtype=f64, device=dev)
+        # server solve: the tile columns of every tile-row pair are divided over nsplit CTAs so that
+        # ~2 CTAs per SM stream the one matrix (a single CTA sustains ~25 GB/s)
+        npairs = (dp // 64 + 1) // 2
+        want = max(1, -(-296 // npairs))
+        self.nsplit = int(min(8, 1 << (want - 1).bit_length())) if dp // 64 >= 8 else 1
+        self.rowpart = torch.empty((Nw + self.nsplit, dp), dtype=f64, device=dev)
         self.colpart = torch.empty((Nw + 1, cpe), dtype=f64, device=dev)
-        self.counters = torch.zeros((Nw + 2,), dtype=torch.int32, device=dev)
+        self.counters = torch.zeros((Nw + 4,), dtype=torch.int32, device=dev)
+        self.zblk = torch.zeros((dp // 64, 2), dtype=f64, device=dev)
         self.ctrl = torch.tensor([1, 0, 1 if stop else 0, 0], dtype=torch.int64, device=dev)
         self.obj_hist = torch.zeros((self.max_iter + 2,), dtype=f64, device=dev)
         self.loss_hist = torch.zeros((self.max_iter + 2,), dtype=f64, device=dev)
@@ -99,17 +101,44 @@ class StarEngine:
         p.rho, p.obj0, p.acc, p.hyy_s = self.rho, float(obj0), float(acc), self.hyy_s
         p.d, p.dp, p.N, p.Nw, p.rank, p.nranks = self.d, dp, self.N, Nw, D.rank, D.world
         p.store, p.max_iter = self.store, self.max_iter
+        p.nsplit, p.zblk = self.nsplit, self.zblk.data_ptr()
         self.launches = 0
         self._graphs = {}
         self.stop = stop
+        if XX is not None:
+            XX = np.asarray(XX, dtype=np.float64)
+            YY = np.asarray(YY, dtype=np.float64).reshape(-1)
+            g0, g1 = int(self.gids[0]), int(self.gids[-1]) + 1
+            X = torch.from_numpy(XX[g0 * s:g1 * s, :d].reshape(Nw, s, d)).to(dev)
+            y = torch.from_numpy(YY[g0 * s:g1 * s].reshape(Nw, s)).to(dev)
+            self.ingest_gram(*LA.gram(X, y, dp), 0)
+            Xs = torch.from_numpy(XX[(N - 1) * s:N * s, :d].reshape(1, s, d)).to(dev)
+            ys = torch.from_numpy(YY[(N - 1) * s:N * s].reshape(1, s)).to(dev)
+            self.ingest_server(*LA.gram(Xs, ys, dp))
         D.barrier()
+
+    # ---- set-up from Gram matrices (scaled configs draw the shards on the device batch by batch)
+    def ingest_gram(self, G, b, hyy, k0: int):
+        """Workers k0..k0+nb of this rank: ``(G_n + rho I)^-1`` packed, ``b_n``, ``0.5 y'y``."""
+        nb = G.shape[0]
+        self.b[k0:k0 + nb] = b
+        self.hyy[k0:k0 + nb] = hyy
+        LA.pack_sym(LA.shifted_inverse(G, self.d, self.rho), self.d, self.store, out=self.P[k0:k0 + nb])
+
+    def ingest_server(self, Gs, bs, hs):
+        """The server's own shard (worker N, replicated on every rank): ``(G_N + (N-1) rho I)^-1``."""
+        LA.pack_sym(LA.shifted_inverse(Gs, self.d, (self.N - 1) * self.rho), self.d, self.store,
+                    out=self.Ps)
+        self.bs.copy_(bs.reshape(-1))
+        self.hyy_s = float(hs.reshape(-1)[0].item())
+        self.p.hyy_s = self.hyy_s
 
     def iterate(self, n, use_graph=True):
         if use_graph and n >= 8:
             self._graph(n).replay()
         else:
             nv.check(nv.lib().gadmm_star_iterate(C.byref(self.p), int(n), nv.stream_ptr()))
-        self.launches += 2 * n
+        self.launches += 4 * n
 
     def _graph(self, n):
         g = self._graphs.get(n)

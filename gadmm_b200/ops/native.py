@@ -149,7 +149,7 @@ class GadmmStar(C.Structure):
         ("rho", C.c_double), ("obj0", C.c_double), ("acc", C.c_double), ("hyy_s", C.c_double),
         ("d", C.c_int), ("dp", C.c_int), ("N", C.c_int), ("Nw", C.c_int), ("rank", C.c_int),
         ("nranks", C.c_int), ("store", C.c_int), ("max_iter", C.c_int), ("nvls", C.c_int),
-        ("server_rank", C.c_int),
+        ("server_rank", C.c_int), ("nsplit", C.c_int), ("reserved", C.c_int), ("zblk", _vp),
     ]
 
 

@@ -253,7 +253,7 @@ int gadmm_dgd_update(const GadmmOwn* p, void* stream);
 int gadmm_dualavg_update(const GadmmOwn* p, int update, void* stream);
 
 /* ---- standard (star) ADMM (K6; standared_ADMM.m:17-107) ------------------------------------
- * Two launches per iteration.  Workers kernel: theta_n = M_n (b_n - lambda_n + rho z) for the
+ * Four launches per iteration (workers, reduce, server stream, z finisher).  Workers kernel: theta_n = M_n (b_n - lambda_n + rho z) for the
  * N-1 workers (lambda_n += rho(theta_n - z) of the previous iteration is folded into the RHS
  * assembly), per-worker objective, and -- by the last CTA -- the reduction
  * u = sum_n (lambda_n + rho theta_n), pushed with P2P stores + a release flag into every GPU.
@@ -292,6 +292,10 @@ typedef struct GadmmStar {
   unsigned long long* const* zflag_peer; /* [nranks] */
   double rho, obj0, acc, hyy_s;
   int d, dp, N, Nw, rank, nranks, store, max_iter, nvls, server_rank;
+  int nsplit;                /* CTAs per tile-row pair of the server solve (0/1 = one); rowpart then
+                                holds [Nw + nsplit][dp] and counters [Nw + 4] */
+  int reserved;
+  double* zblk;              /* [dp/64][2] per-block objective pieces of the server solve */
 } GadmmStar;
 int gadmm_star_iterate(const GadmmStar* p, int n_iter, void* stream);
 

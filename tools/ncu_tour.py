@@ -27,7 +27,7 @@ def main():
     # first-order baselines at 128 workers x d = 2048 (packed Grams 2.1 GB)
     fo, obj0 = build_scaled_first_order(128, 2048, 512)
     alpha = 1.0 / fo.lambda_max(tol=1e-6, max_it=200)
-    Hmax = fo.hmax_per_worker(10)
+    Hmax = fo.hmax_per_worker(10, tol=None)
     thr = 10.0 / (alpha ** 2 * 128 ** 2) / 10
     fo.run_shared(nv.FO_GD, alpha, 0.0, Hmax, 3, obj0, None)
     fo.run_shared(nv.FO_LAG_WK, alpha, thr / 10, Hmax, 3, obj0, None)
