@@ -417,6 +417,19 @@ int gadmm_logi_graph_destroy(void* handle);
  * as the fall-back where conditional nodes are unavailable.  Runs until ctrl[3] or the stop. */
 int gadmm_logi_run_host(const GadmmLogi* p, void* stream);
 
+/* ---- NVLink flag-latency probes (no counterpart in the reference; profiles/flag_latency.md) ----
+ * pingpong: role 0 stores a word + release flag into the peer and waits for the answer, role 1
+ * answers; out_ns[0] = device time of `iters` round trips.  exchange: the all-rank scalar exchange
+ * of the dual/objective kernels (lane q <-> rank q), `iters` times; ring buffers as GadmmChain's
+ * objpart/objflag ([4][nranks]); `base` = last iteration number already used on these flags. */
+int gadmm_probe_pingpong(unsigned long long* my_flag, double* my_word, unsigned long long* peer_flag,
+                         double* peer_word, int iters, int role, unsigned long long* out_ns,
+                         void* stream);
+int gadmm_probe_exchange(double* part, unsigned long long* flag, double* const* part_peer,
+                         unsigned long long* const* flag_peer, int rank, int nranks, int iters,
+                         unsigned long long base, unsigned long long* out_ns, double* out_sum,
+                         void* stream);
+
 /* ---- tensor-core Gram (K1 proper): G[n] (+)= X_n' diag(w_n) X_n with tcgen05 kind::tf32 in a
  * 3-product hi/lo split (fp32-grade), TMA-fed, TMEM accumulators, fp64 result.  X: [N][s][d] fp64
  * or fp32; w: optional [N][s] row weights (logistic Hessian X'DX); work: gadmm_gram_tc_workspace_floats

@@ -128,15 +128,22 @@ def main():
     # chain every iteration (drawn and switched on the device), split run == single-GPU run
     stress = int(os.environ.get("GADMM_STRESS_ITERS", "0"))
     if stress:
-        p0 = np.arange(1, N + 1)
-        sargs = (XX, YY, 1.5, N, d, s, stress, obj0, 0.0, p0, np.ones(N - 1), 1)
+        Ns = int(os.environ.get("GADMM_STRESS_WORKERS", str(N)))      # e.g. 64: >= 2 workers per GPU at 8 GPUs
+        if Ns != N:
+            rs2 = np.random.default_rng(17)
+            XXs, YYs = rs2.standard_normal((Ns * s, d)), rs2.standard_normal(Ns * s)
+            objs = O.opt_sol_closedForm(XXs, YYs)
+        else:
+            XXs, YYs, objs = XX, YY, obj0
+        p0 = np.arange(1, Ns + 1)
+        sargs = (XXs, YYs, 1.5, Ns, d, s, stress, objs, 0.0, p0, np.ones(Ns - 1), 1)
         sm = g.dynamic_group_ADMM_closedForm(*sargs, backend="b200", dist=D, chain_gen="device", rng=5)
         ss = g.dynamic_group_ADMM_closedForm(*sargs, backend="b200", dist=SoloDist(),
                                              chain_gen="device", rng=5)
         assert sm[2] == ss[2] == stress
         np.testing.assert_allclose(sm[0], ss[0], rtol=1e-9, atol=1e-9)
         if D.rank == 0:
-            print(f"STRESS_OK iters={stress} final_gap={sm[1][-1]:.3e} "
+            print(f"STRESS_OK workers={Ns} iters={stress} final_gap={sm[1][-1]:.3e} "
                   f"us_per_iter={1e6 * sm[3][-1] / stress:.1f}")
     D.barrier()
     if D.rank == 0:
