@@ -58,8 +58,8 @@ def free():
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--workers", type=int, default=1024)
-    ap.add_argument("--d", type=int, default=4096)
-    ap.add_argument("--s", type=int, default=1024)
+    ap.add_argument("--dim", dest="d", type=int, default=4096)      # (torchrun's parser trips over --d)
+    ap.add_argument("--samples", dest="s", type=int, default=1024)
     ap.add_argument("--rho", type=float, default=10.0)
     ap.add_argument("--star-rho", type=float, default=1.0)
     ap.add_argument("--tau", type=int, default=10)
