@@ -162,7 +162,7 @@ def group_ADMM_logistic_GD(XX, YY, rho, no_workers, num_feature, per_samples, nu
                                           num_iter, obj0, lambda_logistic, acc, gdStep, **kw)
 
 
-def logReg_GD(X, Y, x, C1, C2, term1, term2, lambda_logistic, gdStep, backend: str = "oracle",
+def logReg_GD(X, Y, x, C1, C2, term1, term2, lambda_logistic, gdStep, backend: str = "auto",
               **kw):
     """``x = logReg_GD(...)`` -- logReg_GD.m:1."""
     b = _resolve(backend)
@@ -259,11 +259,17 @@ def opt_sol_closedForm(XX, YY, backend: str = "auto", **kw):
     return _oracle.opt_sol_closedForm(XX, YY, **kw)
 
 
-def opt_sol(XX, YY, size=None, backend: str = "oracle", **kw):
-    """opt_sol.m:1 (CVX least squares)."""
+def opt_sol(XX, YY, size=None, backend: str = "auto", **kw):
+    """opt_sol.m:1 (CVX least squares; same minimiser as the normal equations)."""
+    if _resolve(backend) == "b200":
+        import numpy as _np
+        X = _np.asarray(XX, dtype=_np.float64)
+        return _engine().opt_sol_closed_form(X[:, : int(size)] if size is not None else X, YY, **kw)
     return _oracle.opt_sol(XX, YY, size, **kw)
 
 
-def opt_sol_logistic(XX, YY, dim, lam, num_workers, backend: str = "oracle", **kw):
-    """opt_sol_logistic.m:1 (CVX in the reference; Newton to 1e-12 here)."""
+def opt_sol_logistic(XX, YY, dim, lam, num_workers, backend: str = "auto", **kw):
+    """opt_sol_logistic.m:1 (CVX in the reference; Newton to 1e-12 here; Newton-CG on the GPU)."""
+    if _resolve(backend) == "b200":
+        return _engine().opt_sol_logistic_gpu(XX, YY, dim, lam, num_workers, **kw)
     return _oracle.opt_sol_logistic(XX, YY, dim, lam, num_workers, **kw)

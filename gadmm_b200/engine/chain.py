@@ -371,24 +371,37 @@ class ChainEngine:
         c = self.desc()
         graphs = {}
 
-        def launch(n):
-            for _ in range(n):
-                nv.check(L.gadmm_rechain(C.byref(r), nv.stream_ptr()))
-                nv.check(L.gadmm_chain_iterate(C.byref(c), 1, nv.stream_ptr()))
+        def launch(it0, n):
+            # iterations it0 .. it0+n-1: the re-chain kernels run only in front of an iteration that
+            # can re-chain (it % tau == 0); the iterations up to the next such point form one
+            # window of gadmm_chain_iterate, i.e. one programmatic-dependent-launch chain
+            i, end = it0, it0 + n
+            while i < end:
+                seg = 1 if tau_i <= 1 else min(end - i, tau_i - (i % tau_i))
+                if tau_i and i > 1 and i % tau_i == 0:
+                    nv.check(L.gadmm_rechain(C.byref(r), nv.stream_ptr()))
+                    self.launches += 2
+                nv.check(L.gadmm_chain_iterate(C.byref(c), int(seg), nv.stream_ptr()))
+                self.launches += (5 if self.split_finish else 3) * seg + 1
+                i += seg
 
-        def iterate(n):
+        def iterate(it0, n):
+            key = (it0 % tau_i if tau_i > 1 else 0, n)
             if n >= 4:
-                g = graphs.get(n)
+                g = graphs.get(key)
                 if g is None:
+                    l0 = self.launches
                     torch.cuda.synchronize(dev)
                     g = torch.cuda.CUDAGraph()
                     with torch.cuda.graph(g):
-                        launch(n)
-                    graphs[n] = g
+                        launch(it0, n)
+                    graphs[key] = (g, self.launches - l0)
+                    self.launches = l0
+                g, cnt = graphs[key]
                 g.replay()
+                self.launches += cnt
             else:
-                launch(n)
-            self.launches += (8 if self.split_finish else 6) * n
+                launch(it0, n)
 
         done, base = 0, 1
         while done < num_iter:
@@ -409,7 +422,7 @@ class ChainEngine:
                 target = num_iter
             while done < target:
                 n = min(window, target - done)
-                iterate(n)
+                iterate(done + 1, n)
                 done += n
                 if self.stop:
                     hit = int(self.ctrl[1].item())

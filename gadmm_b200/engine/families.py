@@ -90,33 +90,3 @@ def dual_averaging_logistic(XX, YY, no_workers, num_feature, noSamples, num_iter
     obj, loss, it, tv, Theta = fo.run_dualavg(alpha, int(num_iter), obj0, acc, jacobi=(mode == "jacobi"))
     res = (obj, loss, it, tv)
     return res + ({"theta": Theta, "iteration": it},) if return_state else res
-
-
-def star_admm(*a, **kw):
-    from .star import star_admm as _s
-    return _s(*a, **kw)
-
-
-def gadmm_logistic_gd(*a, **kw):
-    from .logistic import gadmm_logistic_gd as _f
-    return _f(*a, **kw)
-
-
-def gadmm_logistic_newton(*a, **kw):
-    from .logistic import gadmm_logistic_newton as _f
-    return _f(*a, **kw)
-
-
-def logreg_gd_single(*a, **kw):
-    from .logistic import logreg_gd_single as _f
-    return _f(*a, **kw)
-
-
-def gadmm_logistic_cg(*a, **kw):
-    from .logistic_scaled import gadmm_logistic_cg as _f
-    return _f(*a, **kw)
-
-
-def gadmm_logistic_scaled(*a, **kw):
-    from .logistic_scaled import gadmm_logistic_scaled as _f
-    return _f(*a, **kw)

@@ -123,12 +123,18 @@ def _dynamic(XX, YY, rho, N, d, s, num_iter, obj0, acc, first_path, first_cost, 
 
 def dynamic_gadmm(XX, YY, rho, no_workers, num_feature, noSamples, num_iter, obj0, acc, path,
                   pathCost, coherence_Time, rng=None, rechain=None, store="f64", window=32,
-                  dist=None, return_engine=False, rechain_mode="device", chain_gen="host"):
+                  dist=None, return_engine=False, rechain_mode="device", chain_gen="auto"):
     """D-GADMM with live ``findPath2`` re-chaining (dynamic_group_ADMM_closedForm.m:18-21).
+    ``chain_gen="device"`` (the default unless a ``rechain`` callback supplies the chains):
+    positions come from the Philox generator (seed = ``rng``) and the greedy chains are built on
+    the GPU, one CTA per chain, so a fresh chain every tau iterations costs no host round trip;
     ``chain_gen="host"``: chains are drawn with NumPy on rank 0 and broadcast (bit-identical to
-    the oracle for the same ``rng``); ``chain_gen="device"``: positions come from the Philox
-    generator (seed = ``rng``) and the greedy chains are built on the GPU, one CTA per chain."""
+    the oracle for the same ``rng``; 13 ms per chain at N = 1024)."""
     dist = dist or Dist()
+    if chain_gen == "auto":
+        chain_gen = "host" if rechain is not None else "device"
+    if chain_gen == "device" and isinstance(rng, np.random.Generator):
+        rng = int(rng.integers(2 ** 31 - 1))          # one draw seeds the device generator
     g = np.random.default_rng(rng) if not isinstance(rng, np.random.Generator) else rng
 
     def next_chain(i):

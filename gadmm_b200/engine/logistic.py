@@ -194,13 +194,60 @@ def _gadmm_logistic_gd_dist(XX, YY, rho, N, d, s, num_iter, obj0, lam_log, acc, 
     return res
 
 
-def logreg_gd_single(X, Y, x, C1, C2, term1, term2, lambda_logistic, gdStep, **kw):
-    """``logReg_GD`` for one worker with caller-supplied linear terms.  The GPU kernel
-    (``logistic_half_gd_kernel``) derives those terms from the chain state itself, so this
-    stand-alone helper (a single 50x50 solve, launch-bound on a GPU) evaluates on the host with the
-    oracle's implementation; the batched in-chain solve is :func:`gadmm_logistic_gd`."""
-    from ..oracle import logReg_GD
-    return logReg_GD(X, Y, x, C1, C2, term1, term2, lambda_logistic, gdStep, **kw)
+def logreg_gd_single(X, Y, x, C1, C2, term1, term2, lambda_logistic, gdStep, return_steps=False,
+                     **_kw):
+    """``logReg_GD`` (logReg_GD.m:1-25) for one worker with caller-supplied linear terms, on the GPU:
+    one launch of ``logistic_half_gd_kernel`` (the whole <= 100-step inner loop on chip).  The kernel
+    assembles its frozen term from chain state, ``-lam_{n-1} + lam_n + rho(th_n - th_{n-1}) +
+    rho(th_n - th_{n+1})``; a three-worker chain with ``rho = 1``, ``lam_0 = C1``, ``lam_1 = C2``,
+    ``th_0 = x - term1``, ``th_2 = x - term2`` and the worker in the middle reproduces
+    ``-C1 + C2 + term1 + term2`` exactly as the caller passed it."""
+    dev = torch.device("cuda", torch.cuda.current_device())
+    f64 = torch.float64
+    Xh = np.asarray(X, dtype=np.float64)
+    s, d = Xh.shape
+    dp = nv.padded(d)
+    Xd = torch.from_numpy(np.ascontiguousarray(Xh)).to(dev)
+    yd = torch.from_numpy(np.asarray(Y, dtype=np.float64).reshape(-1).copy()).to(dev)
+
+    def vec(v):
+        out = torch.zeros((dp,), dtype=f64, device=dev)
+        out[:d] = torch.from_numpy(np.asarray(v, dtype=np.float64).reshape(-1).copy()).to(dev)
+        return out
+
+    x0, c1, c2, t1, t2 = vec(x), vec(C1), vec(C2), vec(term1), vec(term2)
+    theta = torch.stack([x0 - t1, x0, x0 - t2]).contiguous()
+    lam = torch.stack([c1, c2, torch.zeros_like(c1)]).contiguous()
+    ctrl = torch.tensor([1, 0, 0, 0], dtype=torch.int64, device=dev)
+    inner = torch.zeros((1,), dtype=torch.int64, device=dev)
+    p = nv.GadmmLogistic()
+    p.X, p.y, p.theta, p.lam = Xd.data_ptr(), yd.data_ptr(), theta.data_ptr(), lam.data_ptr()
+    p.inner_steps, p.ctrl = inner.data_ptr(), ctrl.data_ptr()
+    p.rho, p.lam_log, p.gd_step, p.inner_tol = 1.0, float(lambda_logistic), float(gdStep), 1e-4
+    p.N, p.s, p.d, p.dp, p.max_iter, p.max_inner = 3, int(s), int(d), dp, 1, 100
+    p.n0, p.nloc = 1, 1
+    nv.check(nv.lib().gadmm_logistic_half_gd(C.byref(p), 1, nv.stream_ptr()))
+    torch.cuda.synchronize(dev)
+    out = theta[1, :d].cpu().numpy()
+    return (out, int(inner.item())) if return_steps else out
+
+
+def opt_sol_logistic_gpu(XX, YY, dim, lam, num_workers, tol: float = 1e-12, return_theta=False):
+    """``opt_sol_logistic`` (opt_sol_logistic.m:13-24) on the GPU: the consensus problem
+    ``N lam/2 |x|^2 + sum log(1+exp(-y .* Xx))`` solved by Newton-CG on the one-pass products
+    (all rows as one fp64 shard, so nothing is rounded).  Returns the optimal objective value."""
+    from .logistic_scaled import ScaledLogisticGadmm
+    from ..parallel.runtime import SoloDist
+    XX = np.asarray(XX, dtype=np.float64)[:, : int(dim)]
+    YY = np.asarray(YY, dtype=np.float64).reshape(-1)
+    rows, d = XX.shape
+    dpad = (d + 3) // 4 * 4
+    X = np.zeros((1, rows, dpad), dtype=np.float64)
+    X[0, :, :d] = XX
+    eng = ScaledLogisticGadmm(1, dpad, rows, float(num_workers) * float(lam), 1.0, dist=SoloDist(),
+                              data=(X, YY.reshape(1, rows)), store="f64", max_iter=1)
+    obj0, th = eng.solve_optimum(tol=tol)
+    return (obj0, th[:d].cpu().numpy()) if return_theta else obj0
 
 
 def gadmm_logistic_newton(XX, YY, rho, no_workers, num_feature, per_samples, num_iter, obj0,

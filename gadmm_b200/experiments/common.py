@@ -30,6 +30,18 @@ def add_common_args(ap: argparse.ArgumentParser):
     ap.add_argument("--fig", default=None, help="write the reference's semilogy figure as an .svg file")
 
 
+def optimum_backend(backend: str) -> str:
+    """Backend for the set-up optimum ``obj0``: the GPU path when the run itself is on the GPU
+    engine, the CPU oracle otherwise (nccl / gloo baselines have no optimum solver of their own)."""
+    if backend in (None, "auto"):
+        try:
+            import torch
+            return "b200" if torch.cuda.is_available() else "oracle"
+        except Exception:  # pragma: no cover
+            return "oracle"
+    return "b200" if backend == "b200" else "oracle"
+
+
 def apply_overrides(cfg, args):
     for f in dataclasses.fields(cfg):
         if hasattr(args, f.name) and getattr(args, f.name) is not None:

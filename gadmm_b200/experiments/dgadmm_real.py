@@ -12,7 +12,7 @@ import numpy as np
 from .. import api
 from ..data import split_dataset
 from ..topology import findPath
-from .common import add_common_args, apply_overrides, dataset_or_surrogate, finish
+from .common import add_common_args, apply_overrides, dataset_or_surrogate, finish, optimum_backend
 
 
 @dataclass
@@ -32,7 +32,7 @@ def run(cfg: Config):
     Xd, yd, surrogate = dataset_or_surrogate(cfg.data_dir, "data29", 252, 14, rng)
     X, y, XX, YY, s = split_dataset(Xd, yd, per_split=cfg.per_split)
     N, d = len(X), XX.shape[1]
-    obj0 = api.opt_sol_closedForm(XX, YY, backend="oracle")
+    obj0 = api.opt_sol_closedForm(XX, YY, backend=optimum_backend(cfg.backend))
     base = (XX, YY, cfg.rho, N, d, s, cfg.num_iter, obj0, cfg.acc)
     g = api.group_ADMM_closedForm(*base, backend=cfg.backend)
     path, cost, _ = findPath(N, rng)

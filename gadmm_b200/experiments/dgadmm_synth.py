@@ -14,7 +14,7 @@ from .. import api
 from ..data import linreg_synthetic
 from ..results import with_rechain_overhead
 from ..topology import calc_cost, findPath
-from .common import add_common_args, apply_overrides, dataset_or_surrogate, finish
+from .common import add_common_args, apply_overrides, dataset_or_surrogate, finish, optimum_backend
 
 
 @dataclass
@@ -40,7 +40,7 @@ def run(cfg: Config):
     X, y, Hmax, XX, YY = linreg_synthetic(cfg.num_workers, cfg.num_sample, cfg.growth, rng,
                                           y=ydata[:cfg.num_sample])
     N, s, d = cfg.num_workers, cfg.num_sample, XX.shape[1]
-    obj0 = api.opt_sol_closedForm(XX, YY, backend="oracle")
+    obj0 = api.opt_sol_closedForm(XX, YY, backend=optimum_backend(cfg.backend))
     base = (XX, YY, cfg.rho, N, d, s, cfg.num_iter, obj0, cfg.acc)
     # ---- part A
     path0, cost0, grid = findPath(N, rng)

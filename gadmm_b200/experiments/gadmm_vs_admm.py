@@ -13,7 +13,7 @@ from .. import api
 from ..data import linreg_synthetic
 from ..results import energy_cumulative, star_cost
 from ..topology import findPath2
-from .common import add_common_args, apply_overrides, dataset_or_surrogate, finish
+from .common import add_common_args, apply_overrides, dataset_or_surrogate, finish, optimum_backend
 
 
 @dataclass
@@ -36,7 +36,7 @@ def run(cfg: Config):
     X, y, Hmax, XX, YY = linreg_synthetic(cfg.num_workers, cfg.num_sample, cfg.growth, rng,
                                           y=ydata[:cfg.num_sample])
     N, s, d = cfg.num_workers, cfg.num_sample, XX.shape[1]
-    obj0 = api.opt_sol_closedForm(XX, YY, backend="oracle")
+    obj0 = api.opt_sol_closedForm(XX, YY, backend=optimum_backend(cfg.backend))
     path, pathCost, grid, P_central, center = findPath2(N, rng)
     cost_star, cost_chain = star_cost(P_central), float(np.sum(pathCost))      # :84-87
     base = (XX, YY, cfg.rho, N, d, s, cfg.num_iter, obj0, cfg.acc)

@@ -10,7 +10,7 @@ import numpy as np
 from .. import api
 from ..data import hmax_linear, split_dataset
 from ..results import cumulative_com
-from .common import add_common_args, apply_overrides, baseline_curves, dataset_or_surrogate, finish, gadmm_comm
+from .common import add_common_args, apply_overrides, baseline_curves, dataset_or_surrogate, finish, gadmm_comm, optimum_backend
 
 
 @dataclass
@@ -31,7 +31,7 @@ def run(cfg: Config):
     X, y, XX, YY, s = split_dataset(Xd, yd, per_split=cfg.per_split)
     N, d = len(X), XX.shape[1]
     Hmax = hmax_linear(X)
-    obj0 = api.opt_sol_closedForm(XX, YY, backend="oracle")
+    obj0 = api.opt_sol_closedForm(XX, YY, backend=optimum_backend(cfg.backend))
     curves = {"obj0": np.array([obj0])}
     out = api.GD_DGD_LAG(X, y, N, d, Hmax, cfg.num_iter_baselines, obj0, XX, YY, s,
                          backend=cfg.backend, rng=rng)

@@ -10,7 +10,7 @@ import numpy as np
 from .. import api
 from ..data import linreg_synthetic
 from ..results import cumulative_com
-from .common import add_common_args, apply_overrides, baseline_curves, dataset_or_surrogate, finish, gadmm_comm
+from .common import add_common_args, apply_overrides, baseline_curves, dataset_or_surrogate, finish, gadmm_comm, optimum_backend
 
 
 @dataclass
@@ -33,7 +33,7 @@ def run(cfg: Config):
     X, y, Hmax, XX, YY = linreg_synthetic(cfg.num_workers, cfg.num_sample, cfg.growth, rng,
                                           y=ydata[:cfg.num_sample])
     N, s, d = cfg.num_workers, cfg.num_sample, XX.shape[1]
-    obj0 = api.opt_sol_closedForm(XX, YY, backend="oracle")
+    obj0 = api.opt_sol_closedForm(XX, YY, backend=optimum_backend(cfg.backend))
     curves = {"obj0": np.array([obj0]), "opt_obj": obj0 * np.ones(cfg.num_iter_baselines)}
     out = api.GD_DGD_LAG(X, y, N, d, Hmax, cfg.num_iter_baselines, obj0, XX, YY, s,
                          backend=cfg.backend, rng=rng)
