@@ -378,7 +378,7 @@ class ChainEngine:
             i, end = it0, it0 + n
             while i < end:
                 seg = 1 if tau_i <= 1 else min(end - i, tau_i - (i % tau_i))
-                if tau_i and i > 1 and i % tau_i == 0:
+                if tau_i and i % tau_i == 0:        # (a no-op on the device for iteration 1)
                     nv.check(L.gadmm_rechain(C.byref(r), nv.stream_ptr()))
                     self.launches += 2
                 nv.check(L.gadmm_chain_iterate(C.byref(c), int(seg), nv.stream_ptr()))
