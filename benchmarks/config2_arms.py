@@ -66,7 +66,7 @@ def main():
     ap.add_argument("--cap", type=int, default=320, help="iteration budget of the ADMM family")
     ap.add_argument("--fo-iters", type=int, default=200, help="iteration budget of the first-order family")
     ap.add_argument("--impl", default="b200", choices=["b200", "nccl"])
-    ap.add_argument("--algos", default="gadmm,dgadmm,star,gd,lagps,lagwk,iag,dgd,dualavg")
+    ap.add_argument("--algos", default="gadmm,dgadmm,star,gd,lagps,lagwk,iag,dgd,dualavg,dualavg_jacobi")
     ap.add_argument("--out", default="")
     a = ap.parse_args()
 
@@ -143,7 +143,7 @@ def main():
         free()
 
     # ------------------------------------------------------------------ first-order family
-    fo_list = [x for x in ("gd", "lagps", "lagwk", "iag", "dgd", "dualavg") if x in algos]
+    fo_list = [x for x in ("gd", "lagps", "lagwk", "iag", "dgd", "dualavg", "dualavg_jacobi") if x in algos]
     if fo_list:
         from gadmm_b200.engine.first_order import FirstOrder
         Nl = len(own)
@@ -168,11 +168,14 @@ def main():
                 "lagwk": ("LAG-WK", lambda: fo.run_shared(nv.FO_LAG_WK, alpha, thr / 10, Hmax, T, obj0, None)),
                 "iag": ("cyclic IAG", lambda: fo.run_shared(nv.FO_IAG_CYCLIC, alpha / N, 0.0, Hmax, T, obj0, None)),
                 "dgd": ("DGD", lambda: fo.run_dgd(alpha / 100, T, obj0)),
-                "dualavg": ("dual averaging", lambda: fo.run_dualavg(alpha, T, obj0, 0.0))}
+                "dualavg": ("dual averaging (faithful Gauss-Seidel order)",
+                            lambda: fo.run_dualavg(alpha, T, obj0, 0.0)),
+                "dualavg_jacobi": ("dual averaging (Jacobi order)",
+                                   lambda: fo.run_dualavg(alpha, T, obj0, 0.0, jacobi=True))}
         for key in fo_list:
             name, fn = runs[key]
             r = fn()
-            tv = r[3] if key == "dualavg" else r[2]
+            tv = r[3] if key.startswith("dualavg") else r[2]
             tvt = torch.as_tensor(np.asarray(tv), device=dev)
             if world > 1:
                 torch.distributed.all_reduce(tvt, op=torch.distributed.ReduceOp.MAX)

@@ -241,7 +241,7 @@ def run_arms(a, D, obj0, Gsum, algos, record, hbm):
                {"rho": a.star_rho})
         gc.collect()
         torch.cuda.empty_cache()
-    fo = [x for x in ("gd", "lagps", "lagwk", "iag", "dgd", "dualavg") if x in algos]
+    fo = [x for x in ("gd", "lagps", "lagwk", "iag", "dgd", "dualavg_jacobi") if x in algos]
     if fo:
         W = DenseWorkers(own, d, s, D)
         lmax = float(torch.linalg.eigvalsh(Gsum[:d, :d])[-1].item())
@@ -255,10 +255,10 @@ def run_arms(a, D, obj0, Gsum, algos, record, hbm):
         _allsum(hm, world)
         Hmax = hm.cpu().numpy()
         names = {"gd": "GD", "lagps": "LAG-PS", "lagwk": "LAG-WK", "iag": "cyclic IAG", "dgd": "DGD",
-                 "dualavg": "dual averaging (Jacobi order)"}
+                 "dualavg_jacobi": "dual averaging (Jacobi order)"}
         for key in fo:
             extra = {"step": alpha}
-            if key in ("dgd", "dualavg"):
+            if key in ("dgd", "dualavg_jacobi"):
                 loss, tv = run_chain_first_order(W, key, N, d, alpha / 100 if key == "dgd" else alpha,
                                                  a.fo_iters, obj0, D)
             else:
