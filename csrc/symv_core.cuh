@@ -97,10 +97,53 @@ __device__ bool symv_cta(SymvSmem<T, NSTAGES>& sm, const T* __restrict__ S, int 
 #ifndef GADMM_XPREFETCH
 #define GADMM_XPREFETCH 0
 #endif
+#ifndef GADMM_XPIPE
+#define GADMM_XPIPE 1
+#endif
     constexpr int kXG = 4;
     int stage = 0;
     uint32_t phase = 0;
-#if !GADMM_XPREFETCH
+#if GADMM_XPIPE
+    // One-deep software pipeline over the tiles of BOTH tile-rows: the bulk copy of tile t and the
+    // global loads of its RHS slice are issued first, then the slice of tile t-1 (whose loads
+    // have had a whole tile period to land) is written to shared memory and tile t-1 is handed
+    // to the consumers.  Without it every tile costs one L2 round trip of the fused RHS assembly
+    // between two bulk copies (~0.8 us): harmless with 32 KiB fp64 tiles, but it caps a CTA at
+    // ~20 GB/s with 16 KiB fp32 tiles.
+    {
+      double pend0 = 0.0, pend1 = 0.0;
+      int pend_stage = -1;
+      for (int rr = 0; rr < nrows; ++rr) {
+        const int I = rr == 0 ? rowA : rowB;
+        const int Jb = (int)(((long long)(I + 1) * part) / nparts);
+        const int Je = (int)(((long long)(I + 1) * (part + 1)) / nparts);
+        sm.xrow[rr][lane] = xf(I * kT + lane);
+        sm.xrow[rr][lane + 32] = xf(I * kT + lane + 32);
+        const T* rowbase = S + ((size_t)I * (I + 1) / 2) * (kT * kT);
+        for (int J = Jb; J < Je; ++J) {
+          mbar_wait(&sm.empty[stage], phase ^ 1);
+          if (lane == 0) bulk_g2s(sm.tile[stage], rowbase + (size_t)J * (kT * kT), kTileBytes, &sm.full[stage]);
+          const double x0 = xf(J * kT + lane), x1 = xf(J * kT + lane + 32);   // in flight
+          if (pend_stage >= 0) {
+            sm.xs[pend_stage][lane] = pend0;
+            sm.xs[pend_stage][lane + 32] = pend1;
+            __syncwarp();
+            if (lane == 0) mbar_arrive_expect_tx(&sm.full[pend_stage], kTileBytes);
+          }
+          pend0 = x0;
+          pend1 = x1;
+          pend_stage = stage;
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+      if (pend_stage >= 0) {
+        sm.xs[pend_stage][lane] = pend0;
+        sm.xs[pend_stage][lane + 32] = pend1;
+        __syncwarp();
+        if (lane == 0) mbar_arrive_expect_tx(&sm.full[pend_stage], kTileBytes);
+      }
+    }
+#elif !GADMM_XPREFETCH
     for (int rr = 0; rr < nrows; ++rr) {
       const int I = rr == 0 ? rowA : rowB;
       const int Jb = (int)(((long long)(I + 1) * part) / nparts);

@@ -197,11 +197,18 @@ class FirstOrder:
 
     @staticmethod
     def _time(t_hist, n):
+        if n <= 0:
+            return np.zeros(0)
         t = t_hist[1:n + 1].to(torch.float64)
-        return ((t - t[0]) * 1e-9).cpu().numpy() if n > 0 else np.zeros(0)
+        live = t > 0                                # iterations restored from a checkpoint: no clock
+        t0 = t[live][0] if bool(live.any()) else t[0]
+        return torch.clamp((t - t0) * 1e-9, min=0.0).cpu().numpy()
 
     def run_shared(self, kind, step, thr, Hmax, T, obj0, accuracy=None, uni=None, cumprob=None,
-                   window=256):
+                   window=256, state=None, return_state=False):
+        """GD / LAG-PS / LAG-WK / IAG.  ``state`` (from an earlier ``return_state=True`` call of the
+        same method and partition) resumes after its last iteration; ``T`` is the absolute last
+        iteration.  The state is appended to the returned tuple with ``return_state=True``."""
         N, dp, dev = self.N, self.dp, self.dev
         f64 = torch.float64
         theta = torch.zeros((dp,), dtype=f64, device=dev)
@@ -212,6 +219,16 @@ class FirstOrder:
         obj_h, loss_h, comm_h, t_h = self._hist(T)
         ctrl = torch.tensor([1, 0, 1 if accuracy is not None else 0, 1], dtype=torch.int64, device=dev)
         cnt = torch.zeros((2,), dtype=torch.int32, device=dev)
+        done0 = 0
+        if state is not None:
+            done0 = int(state["iteration"])
+            theta.copy_(torch.as_tensor(state["theta"], device=dev))
+            ghat.copy_(torch.as_tensor(state["ghat"], device=dev))
+            that.copy_(torch.as_tensor(state["theta_hat"], device=dev))
+            dnorm.copy_(torch.as_tensor(state["dnorm"], device=dev))
+            ctrl[0], ctrl[3] = done0 + 1, int(state["comm_iter"])
+            for h, key in ((obj_h, "obj"), (loss_h, "loss"), (comm_h, "comm")):
+                h[1:done0 + 1] = torch.as_tensor(np.asarray(state[key][:done0]), device=dev)
         hm = torch.as_tensor(np.asarray(Hmax, dtype=np.float64).reshape(-1)[self.gid0:self.gid0 + N]
                              .copy(), device=dev)
         un = torch.as_tensor(np.asarray(uni if uni is not None else np.zeros(T + 2)), dtype=f64,
@@ -258,24 +275,39 @@ class FirstOrder:
             nv.check(L.gadmm_shared_update(C.byref(p), nv.stream_ptr()))
             self.launches += 2 if split else 1
 
-        self._drive(body, ctrl, T, accuracy is not None, window)
+        self._drive(body, ctrl, T - done0, accuracy is not None, window)
         hit = int(ctrl[1].item())
         n = hit if hit else T
         if self.dist is not None:
             self.dist.barrier()
+        res = (obj_h[1:n + 1].cpu().numpy(), loss_h[1:n + 1].cpu().numpy(), self._time(t_h, n),
+               comm_h[1:n + 1].cpu().numpy(), theta[:self.d].cpu().numpy())
+        if return_state:
+            it = int(ctrl[0].item()) - 1
+            res = res + ({"iteration": it, "theta": theta.cpu().numpy(), "ghat": ghat.cpu().numpy(),
+                          "theta_hat": that.cpu().numpy(), "dnorm": dnorm.cpu().numpy(),
+                          "comm_iter": int(ctrl[3].item()), "obj": obj_h[1:it + 1].cpu().numpy(),
+                          "loss": loss_h[1:it + 1].cpu().numpy(),
+                          "comm": comm_h[1:it + 1].cpu().numpy(), "gid0": self.gid0},)
         keep = (theta, ghat, that, dnorm, hm, un, cp, cnt, sym, xbuf, xflag, xb_peer, xf_peer,
                 dnpart, cnt2)                               # alive until here
         del keep
-        return (obj_h[1:n + 1].cpu().numpy(), loss_h[1:n + 1].cpu().numpy(), self._time(t_h, n),
-                comm_h[1:n + 1].cpu().numpy(), theta[:self.d].cpu().numpy())
+        return res
 
-    def _own(self, step, T, obj0, acc, stop, jacobi=0):
+    def _own(self, step, T, obj0, acc, stop, jacobi=0, state=None):
         N, dp, dev = self.N, self.dp, self.dev
         f64 = torch.float64
         Theta = torch.zeros((N, dp), dtype=f64, device=dev)
         Z = torch.zeros((N, dp), dtype=f64, device=dev)
         obj_h, loss_h, _, t_h = self._hist(T)
         ctrl = torch.tensor([1, 0, 1 if stop else 0, 0], dtype=torch.int64, device=dev)
+        if state is not None:                       # resume (single-GPU runs)
+            it0 = int(state["iteration"])
+            Theta.copy_(torch.as_tensor(state["Theta"], device=dev))
+            Z.copy_(torch.as_tensor(state["Z"], device=dev))
+            ctrl[0] = it0 + 1
+            obj_h[1:it0 + 1] = torch.as_tensor(np.asarray(state["obj"][:it0]), device=dev)
+            loss_h[1:it0 + 1] = torch.as_tensor(np.asarray(state["loss"][:it0]), device=dev)
         cnt = torch.zeros((1,), dtype=torch.int32, device=dev)
         p = nv.GadmmOwn()
         p.Theta, p.Y, p.fw, p.Z = Theta.data_ptr(), self.Y.data_ptr(), self.fw.data_ptr(), Z.data_ptr()
@@ -310,8 +342,17 @@ class FirstOrder:
         self._own_keep = keep
         return p, Theta, Z, obj_h, loss_h, t_h, ctrl, cnt
 
-    def run_dgd(self, step, T, obj0, window=256):
-        p, Theta, Z, obj_h, loss_h, t_h, ctrl, cnt = self._own(step, T, obj0, 0.0, False)
+    def _own_state(self, Theta, Z, ctrl, obj_h, loss_h):
+        it = int(ctrl[0].item()) - 1
+        return {"iteration": it, "Theta": Theta.cpu().numpy(), "Z": Z.cpu().numpy(),
+                "obj": obj_h[1:it + 1].cpu().numpy(), "loss": loss_h[1:it + 1].cpu().numpy(),
+                "gid0": self.gid0}
+
+    def run_dgd(self, step, T, obj0, window=256, state=None, return_state=False):
+        if state is not None and self.dist is not None:
+            raise ValueError("DGD resume is implemented for single-GPU runs")
+        p, Theta, Z, obj_h, loss_h, t_h, ctrl, cnt = self._own(step, T, obj0, 0.0, False, state=state)
+        done0 = int(state["iteration"]) if state is not None else 0
         L = nv.lib()
 
         def body():
@@ -320,13 +361,19 @@ class FirstOrder:
             nv.check(L.gadmm_dgd_update(C.byref(p), nv.stream_ptr()))
             self.launches += 2 if p.nranks > 1 else 1
 
-        self._drive(body, ctrl, T, False, window)
+        self._drive(body, ctrl, T - done0, False, window)
         if self.dist is not None:
             self.dist.barrier()
-        return obj_h[1:T + 1].cpu().numpy(), loss_h[1:T + 1].cpu().numpy(), self._time(t_h, T)
+        res = (obj_h[1:T + 1].cpu().numpy(), loss_h[1:T + 1].cpu().numpy(), self._time(t_h, T))
+        return res + (self._own_state(Theta, Z, ctrl, obj_h, loss_h),) if return_state else res
 
-    def run_dualavg(self, alpha, T, obj0, acc, jacobi=False, window=256):
-        p, Theta, Z, obj_h, loss_h, t_h, ctrl, cnt = self._own(alpha, T, obj0, acc, True, jacobi)
+    def run_dualavg(self, alpha, T, obj0, acc, jacobi=False, window=256, state=None,
+                    return_state=False):
+        if state is not None and self.dist is not None:
+            raise ValueError("dual-averaging resume is implemented for single-GPU runs")
+        p, Theta, Z, obj_h, loss_h, t_h, ctrl, cnt = self._own(alpha, T, obj0, acc, True, jacobi,
+                                                                state=state)
+        done0 = int(state["iteration"]) if state is not None else 0
         L = nv.lib()
 
         def body():
@@ -335,7 +382,7 @@ class FirstOrder:
             nv.check(L.gadmm_dualavg_update(C.byref(p), 1, nv.stream_ptr()))
             self.launches += 2 if p.nranks > 1 else 1
 
-        self._drive(body, ctrl, T, True, window)
+        self._drive(body, ctrl, T - done0, True, window)
         if not int(ctrl[1].item()):
             # close the last iteration: objective of the final iterate
             self.provider(Theta, self.dp)
@@ -351,5 +398,6 @@ class FirstOrder:
             self.dist.all_reduce_sum_(full)
             self.dist.barrier()
             th = full
-        return (obj_h[1:n + 1].cpu().numpy(), loss_h[1:n + 1].cpu().numpy(), n, self._time(t_h, n),
-                th.cpu().numpy().T)
+        res = (obj_h[1:n + 1].cpu().numpy(), loss_h[1:n + 1].cpu().numpy(), n, self._time(t_h, n),
+               th.cpu().numpy().T)
+        return res + (self._own_state(Theta, Z, ctrl, obj_h, loss_h),) if return_state else res

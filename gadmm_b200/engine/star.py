@@ -156,7 +156,7 @@ class StarEngine:
         T = self.max_iter if num_iter is None else min(int(num_iter), self.max_iter)
         if T >= 8:
             self._graph(min(window, T))        # capture before the clock starts
-        done = 0
+        done = getattr(self, "_done", 0)       # > 0 after load_state()
         while done < T:
             n = min(window, T - done)
             self.iterate(n)
@@ -171,17 +171,66 @@ class StarEngine:
         obj = self.obj_hist[1:Iter + 1].cpu().numpy()
         loss = self.loss_hist[1:Iter + 1].cpu().numpy()
         t = self.t_hist[1:Iter + 1].to(torch.float64)
-        tv = (t - t[0]) * 1e-9
+        live = t > 0                                # restored iterations carry no clock
+        t0 = t[live][0] if bool(live.any()) else t[0]
+        tv = torch.clamp((t - t0) * 1e-9, min=0.0)
         if self.dist.world > 1:
             import torch.distributed as dist
             dist.all_reduce(tv, op=dist.ReduceOp.MAX)
         return obj, loss, Iter, tv.cpu().numpy()
 
 
+    # ------------------------------------------------------------------ checkpoint / resume
+    def state(self):
+        """Solver state: this rank's worker models and duals, the consensus
+        model z, the iteration, the curves.  ``dual`` is the reference's lambda_n after the dual
+        update of the last iteration (the kernel itself folds that update into the next solve)."""
+        torch.cuda.synchronize(self.dev)
+        it = int(self.ctrl[0].item()) - 1
+        d = self.d
+        lam_ref = self.lam + self.rho * (self.theta - self.z.unsqueeze(0))
+        return {"theta": self.theta[:, :d].cpu().numpy().T.copy(), "z": self.z[:d].cpu().numpy().copy(),
+                "dual": lam_ref[:, :d].cpu().numpy().T.copy(),
+                "lam_lagged": self.lam[:, :d].cpu().numpy().T.copy(),
+                "g0": int(self.gids[0]), "iteration": it,
+                "obj": self.obj_hist[1:it + 1].cpu().numpy().copy(),
+                "loss": self.loss_hist[1:it + 1].cpu().numpy().copy(), "rho": self.rho}
+
+    def load_state(self, st):
+        """Resume from :meth:`state` (same partition): the next iteration is ``iteration + 1``."""
+        it, d = int(st["iteration"]), self.d
+
+        def dev_t(a):
+            return torch.as_tensor(np.asarray(a, dtype=np.float64).T.copy(), device=self.dev)
+
+        self.theta.zero_()
+        self.lam.zero_()
+        self.z.zero_()
+        self.theta[:, :d] = dev_t(st["theta"])
+        self.lam[:, :d] = dev_t(st["lam_lagged"])
+        self.z[:d] = torch.as_tensor(np.asarray(st["z"], dtype=np.float64), device=self.dev)
+        n = min(it, len(st.get("obj", [])))
+        if n:
+            self.obj_hist[1:n + 1] = torch.as_tensor(np.asarray(st["obj"][:n]), device=self.dev)
+            self.loss_hist[1:n + 1] = torch.as_tensor(np.asarray(st["loss"][:n]), device=self.dev)
+        self.uflag.zero_()
+        self.zflag.zero_()
+        self.ctrl[0] = it + 1
+        self.ctrl[1] = 0
+        self._done = it
+        torch.cuda.synchronize(self.dev)
+        self.dist.barrier()
+
+
 def star_admm(XX, YY, rho, no_workers, num_feature, noSamples, num_iter, obj0, acc, store="f64",
-              dist=None, window=64, return_engine=False, nvls="auto"):
+              dist=None, window=64, return_engine=False, nvls="auto", state=None,
+              return_state=False):
     eng = StarEngine(XX, YY, rho, no_workers, num_feature, noSamples, num_iter, obj0, acc, dist=dist,
                      store=store, nvls=nvls)
+    if state is not None:
+        eng.load_state(state)
     it = eng.run(num_iter, window=window)
     res = eng.results(it)
+    if return_state:
+        res = res + (eng.state(),)
     return res + (eng,) if return_engine else res

@@ -81,3 +81,43 @@ def test_dual_averaging_stops_early():
     b = g.dual_averaging(*args, backend="b200")
     assert a[2] == b[2] and b[0].shape == (b[2],)
     np.testing.assert_allclose(a[0], b[0], rtol=1e-9)
+
+
+def test_checkpoint_resume_star_and_first_order():
+    """state after a partial run -> resumed run continues the uninterrupted curve bit for bit
+    (star ADMM, LAG-WK, DGD, dual averaging): SURVEY.md section 5.4."""
+    from gadmm_b200.engine.first_order import FirstOrder
+    from gadmm_b200.engine.star import star_admm
+    from gadmm_b200.ops import native as nv
+    rng = np.random.default_rng(21)
+    N, s, d = 7, 20, 14
+    XX = rng.standard_normal((N * s, d))
+    YY = XX @ rng.standard_normal(d) + 0.1 * rng.standard_normal(N * s)
+    obj0 = O.opt_sol_closedForm(XX, YY)
+    full = star_admm(XX, YY, 1.0, N, d, s, 90, obj0, 0.0)
+    part = star_admm(XX, YY, 1.0, N, d, s, 35, obj0, 0.0, return_state=True)
+    st = part[4]
+    assert st["iteration"] == 35 and st["theta"].shape == (d, N - 1)
+    rest = star_admm(XX, YY, 1.0, N, d, s, 90, obj0, 0.0, state=st)
+    assert rest[2] == 90
+    np.testing.assert_array_equal(rest[0], full[0])
+    o = O.standared_ADMM(XX, YY, 1.0, N, d, s, 35, obj0, 0.0)
+    np.testing.assert_allclose(o[0], part[0], rtol=1e-9)
+
+    fo = FirstOrder(XX, YY, N, d, s)
+    alpha = 1.0 / fo.lambda_max()
+    Hmax = fo.hmax_per_worker()
+    thr = 1.0 / (alpha ** 2 * N ** 2) / 10
+    a = fo.run_shared(nv.FO_LAG_WK, alpha, thr, Hmax, 120, obj0, None)
+    b = fo.run_shared(nv.FO_LAG_WK, alpha, thr, Hmax, 50, obj0, None, return_state=True)
+    c = fo.run_shared(nv.FO_LAG_WK, alpha, thr, Hmax, 120, obj0, None, state=b[5])
+    np.testing.assert_array_equal(a[0], c[0])
+    np.testing.assert_array_equal(a[3], c[3])                   # upload counters continue
+    a = fo.run_dgd(alpha / 100, 80, obj0)
+    b = fo.run_dgd(alpha / 100, 30, obj0, return_state=True)
+    c = fo.run_dgd(alpha / 100, 80, obj0, state=b[3])
+    np.testing.assert_array_equal(a[0], c[0])
+    a = fo.run_dualavg(alpha, 80, obj0, 0.0)
+    b = fo.run_dualavg(alpha, 30, obj0, 0.0, return_state=True)
+    c = fo.run_dualavg(alpha, 80, obj0, 0.0, state=b[5])
+    np.testing.assert_array_equal(a[0], c[0])
