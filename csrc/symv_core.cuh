@@ -97,8 +97,11 @@ __device__ bool symv_cta(SymvSmem<T, NSTAGES>& sm, const T* __restrict__ S, int 
 #ifndef GADMM_XPREFETCH
 #define GADMM_XPREFETCH 0
 #endif
+// One-deep software pipeline of the RHS slice loads (GADMM_XPIPE=1): same-box A/B at 128 workers x
+// d=4096 per GPU: fp64 tiles 1.3099 vs 1.3096 ms, fp32 tiles 0.785 vs 0.775 ms per iteration --
+// the producer is not the limiter (the per-tile cross-warp column reduction is), so it is off.
 #ifndef GADMM_XPIPE
-#define GADMM_XPIPE 1
+#define GADMM_XPIPE 0
 #endif
     constexpr int kXG = 4;
     int stage = 0;
