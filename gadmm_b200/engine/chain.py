@@ -42,7 +42,17 @@ class ChainEngine:
         self.N, self.d, self.rho = int(N), int(d), float(rho)
         self.dp = nv.padded(self.d)
         self.obj0, self.acc, self.max_iter = float(obj0), float(acc), int(max_iter)
+        # store="mixed": iterate on fp32-stored inverses (half the bytes per iteration) until the
+        # estimated gap is small, then switch to the fp64 inverses, whose objective / stop test are
+        # exact (see switch_to_f64); both sets are kept.
+        self.mixed = store == "mixed"
         self.store = nv.STORE_F64 if store in ("f64", "fp64", nv.STORE_F64) else nv.STORE_F32
+        if store == "f32" and stop:
+            import warnings
+            warnings.warn("store='f32': the reported objective uses G theta = r - c rho theta, which "
+                          "is only first-order accurate with fp32 inverses (error ~ cond(A) x 6e-8 "
+                          "relative); the stop test is unreliable -- use store='mixed' or 'f64'",
+                          stacklevel=3)
         self.dynamic = dynamic
         self.stop = stop
         self.pdl = bool(pdl) and os.environ.get("GADMM_B200_NO_PDL") != "1"
@@ -124,8 +134,12 @@ class ChainEngine:
             self.P[1] = torch.empty((Nloc, pe), dtype=dt, device=dev)
         else:
             self.P_end = {}   # local index -> (1, pe) tensor for chain-end workers (c=1)
+        if self.mixed:        # the fp64 twins, used after switch_to_f64()
+            self.P64 = {c: torch.empty((Nloc, pe), dtype=f64, device=dev) for c in self.P}
+            self.P64_end = {}
+            self.P32, self.P32_end = self.P, getattr(self, "P_end", None)
         self.ctrl[0] = 1
-        self.ctrl[2] = 1 if self.stop else 0
+        self.ctrl[2] = 1 if (self.stop and not self.mixed) else 0   # mixed: stop test after the switch
         self.ctrl[3] = -1          # first-crossing register of the persistent kernel (= ~0)
         self.objring = torch.zeros((32 * Nloc,), dtype=f64, device=dev)
         self.ringcnt = torch.zeros((32,), dtype=i32, device=dev)
@@ -158,9 +172,13 @@ class ChainEngine:
         self.hyy[k0:k0 + nb] = hyy
         A = LA.shifted_inverse(G, self.d, 2.0 * self.rho)
         LA.pack_sym(A, self.d, self.store, out=self.P[2][k0:k0 + nb])
+        if self.mixed:
+            LA.pack_sym(A, self.d, nv.STORE_F64, out=self.P64[2][k0:k0 + nb])
         if self.dynamic:
             A = LA.shifted_inverse(G, self.d, 1.0 * self.rho, out=A)
             LA.pack_sym(A, self.d, self.store, out=self.P[1][k0:k0 + nb])
+            if self.mixed:
+                LA.pack_sym(A, self.d, nv.STORE_F64, out=self.P64[1][k0:k0 + nb])
         else:
             self._G_keep = getattr(self, "_G_keep", {})
             # keep the Gram of potential chain ends (first / last worker id) for the c=1 inverse
@@ -215,6 +233,8 @@ class ChainEngine:
                             "chain -- construct the engine with dynamic=True")
                     A = LA.shifted_inverse(self._G_keep[k], self.d, 1.0 * self.rho)
                     self.P_end[k] = LA.pack_sym(A, self.d, self.store)
+                    if self.mixed:
+                        self.P64_end[k] = LA.pack_sym(A, self.d, nv.STORE_F64)
                 mp[k] = self.P_end[k].data_ptr()
         self.tab.copy_(th, non_blocking=True)
         self.Mptr.copy_(mp, non_blocking=True)
@@ -251,6 +271,28 @@ class ChainEngine:
             self.flags[nb] = max(int(self.flags[nb].item()), ver)
         torch.cuda.synchronize(self.dev)
         self.dist.barrier()
+
+    def switch_to_f64(self):
+        """``store="mixed"``: from the next iteration on use the fp64 inverses.  Models and duals
+        carry over (any (theta, nu) is a valid GADMM state); from here the objective identity is
+        exact and the stop test is enabled.  Stream-ordered; captured graphs are dropped."""
+        if not self.mixed or self.store == nv.STORE_F64:
+            return
+        self.store = nv.STORE_F64
+        self.P = self.P64
+        if not self.dynamic:
+            self.P_end = self.P64_end
+        self._desc = None
+        self._graphs = {}
+        self.ctrl[2] = 1 if self.stop else 0
+        if self.path0 is not None:
+            prev, self.path0 = self.path0, None      # (no neighbour gather: same chain)
+            self.set_path(prev)
+
+    def _mixed_ready(self, switch_tol: float) -> bool:
+        """True when the (estimated) gap of the last completed iteration is below ``switch_tol``."""
+        it = int(self.ctrl[0].item()) - 1
+        return it >= 1 and float(self.loss_hist[it].item()) < switch_tol
 
     # ---------------------------------------------------------------------------- descriptor
     def desc(self) -> nv.GadmmChain:
@@ -307,11 +349,19 @@ class ChainEngine:
             self._graphs[n_iter] = g        # capture does not execute anything
         return g
 
+    def _switch_tol(self, switch_tol):
+        if switch_tol is not None:
+            return float(switch_tol)
+        return max(1e3 * self.acc, 1e-5 * abs(self.obj0))
+
     def run(self, num_iter: Optional[int] = None, window: int = 32, rechain=None,
-            coherence: Optional[float] = None, use_graph: bool = True) -> int:
+            coherence: Optional[float] = None, use_graph: bool = True,
+            switch_tol: Optional[float] = None) -> int:
         """Run until the stop test fires or ``num_iter`` iterations are done.  ``rechain(i)``
         returns the 0-based chain installed before iteration ``i`` when ``i % coherence == 0``
-        (dynamic_group_ADMM_closedForm.m:18-21).  Returns ``Iter``."""
+        (dynamic_group_ADMM_closedForm.m:18-21).  ``store="mixed"``: fp32 inverses until the
+        estimated gap is below ``switch_tol`` (default max(1e3 acc, 1e-5 |obj0|), checked once per
+        window), fp64 inverses and the exact stop test from there.  Returns ``Iter``."""
         num_iter = self.max_iter if num_iter is None else min(int(num_iter), self.max_iter)
         nv.lib().gadmm_chain_configure()
         done = getattr(self, "_resume_from", 0)
@@ -331,6 +381,10 @@ class ChainEngine:
                 n = max(1, min(n, nxt - it_next))
             self.iterate(n, use_graph=use_graph)
             done += n
+            if self.mixed and self.store == nv.STORE_F32 and \
+                    self._mixed_ready(self._switch_tol(switch_tol)):
+                self.switch_to_f64()
+                self.switched_at = done
             if self.stop:
                 hit = int(self.ctrl[1].item())      # host sync once per window
                 if hit:
@@ -339,7 +393,7 @@ class ChainEngine:
 
     # ------------------------------------------------------- D-GADMM with device-side re-chaining
     def run_device_rechain(self, num_iter, chain_source, tau, window: int = 32, chunk: int = 256,
-                           chunk_source=None):
+                           chunk_source=None, switch_tol: Optional[float] = None):
         """D-GADMM without the host in the loop: the chains of the coming windows are uploaded in
         chunks of ``chunk`` rows; two tiny kernels in front of every head kernel switch tables and
         pull the new remote neighbours' theta over NVLink when ``it % tau == 0`` (csrc/rechain.cu).
@@ -424,6 +478,24 @@ class ChainEngine:
                 n = min(window, target - done)
                 iterate(done + 1, n)
                 done += n
+                if self.mixed and self.store == nv.STORE_F32 and \
+                        self._mixed_ready(self._switch_tol(switch_tol)):
+                    torch.cuda.synchronize(dev)
+                    # same chain tables (they live on the device), fp64 inverses from here on
+                    self.store, self.P = nv.STORE_F64, self.P64
+                    self._desc = None
+                    self.ctrl[2] = 1 if self.stop else 0
+                    r.base_c1, r.base_c2 = self.P[1].data_ptr(), self.P[2].data_ptr()
+                    r.stride_bytes = self.P[2].stride(0) * self.P[2].element_size()
+                    # pointer table: same workers, same c, other base
+                    off = self.Mptr - self.P32[2].data_ptr()
+                    is1 = (off < 0) | (off >= self.P32[2].numel() * 4)
+                    k = torch.arange(self.Nloc, device=dev)
+                    self.Mptr.copy_(torch.where(is1, self.P[1].data_ptr() + k * r.stride_bytes,
+                                                self.P[2].data_ptr() + k * r.stride_bytes))
+                    c = self.desc()
+                    graphs.clear()
+                    self.switched_at = done
                 if self.stop:
                     hit = int(self.ctrl[1].item())
                     if hit:
@@ -574,9 +646,16 @@ class ChainEngine:
                   self.fin_counters, self.wready, self.objw, self.obj_hist, self.loss_hist,
                   self.t_hist, self.ringcnt, self.nuflag, self.sync):
             t.zero_()
+        if self.mixed:                      # back to the fp32 phase
+            self.store, self.P = nv.STORE_F32, self.P32
+            if not self.dynamic:
+                self.P_end = self.P32_end
+            if self.path0 is not None:
+                prev, self.path0 = self.path0, None
+                self.set_path(prev)
         self.ctrl.zero_()
         self.ctrl[0] = 1
-        self.ctrl[2] = 1 if self.stop else 0
+        self.ctrl[2] = 1 if (self.stop and not self.mixed) else 0
         self.ctrl[3] = -1
         self._resume_from = 0
         self._desc = None

@@ -184,3 +184,31 @@ def test_state_after_early_stop_is_the_state_of_iter(d):
     full = g.group_ADMM_closedForm(*args, more, obj0, 0.0, backend="b200")
     rest = g.group_ADMM_closedForm(*args, more, obj0, 0.0, backend="b200", state=st)
     np.testing.assert_allclose(rest[0][b[2]:], full[0][b[2]:], rtol=1e-12)
+
+
+def test_mixed_storage_switches_to_fp64_and_stops_exactly():
+    """store="mixed": fp32-stored inverses while the gap is large (half the bytes per iteration,
+    objective only estimated), fp64 inverses -- exact objective identity and stop test -- once the
+    estimated gap is below the switch tolerance.  The run must stop where the true gap is below
+    acc, within a couple of iterations of the all-fp64 run."""
+    import warnings
+    rng = np.random.default_rng(3)
+    N, s, d = 6, 40, 150
+    XX = rng.standard_normal((N * s, d))
+    YY = XX @ rng.standard_normal(d) + 0.1 * rng.standard_normal(N * s)
+    obj0 = O.opt_sol_closedForm(XX, YY)
+    args = (XX, YY, 2.0, N, d, s, 3000, obj0, 1e-6)
+    a = O.group_ADMM_closedForm(*args)
+    b = g.group_ADMM_closedForm(*args, backend="b200", store="mixed", return_engine=True)
+    eng = b[-1]
+    assert 0 < eng.switched_at < b[2]
+    assert abs(a[2] - b[2]) <= 3, (a[2], b[2])
+    assert b[1][-1] < 1e-6
+    # the final objective is exact (fp64 identity), not an fp32 estimate
+    th = eng.state()["theta"]
+    true = sum(0.5 * np.sum((XX[n * s:(n + 1) * s] @ th[:, n] - YY[n * s:(n + 1) * s]) ** 2) for n in range(N))
+    assert abs(true - b[0][-1]) <= 1e-9 * max(1.0, abs(true))
+    with warnings.catch_warnings(record=True) as w:          # plain fp32 storage + stop test: warned
+        warnings.simplefilter("always")
+        g.group_ADMM_closedForm(*args[:6], 20, obj0, 1e-6, backend="b200", store="f32")
+        assert any("first-order" in str(x.message) for x in w)
