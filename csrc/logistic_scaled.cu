@@ -16,6 +16,8 @@
 #include "../include/gadmm_b200.h"
 #include "common.cuh"
 
+#include <cooperative_groups.h>
+
 namespace gadmm {
 
 constexpr int LS_THREADS = 256;
@@ -412,6 +414,7 @@ static int xtwx_entry(const void* X, int store, const double* y, const double* x
 // per-row scalars live in global memory; "any row ..." decisions are taken by the last CTA
 // (atomic ticket) which also sets the WHILE condition of the enclosing graph loop.
 // =============================================================================================
+constexpr int LG_CL = 4;      // CTAs (one thread-block cluster) per row in the CG / line-search steps
 constexpr int LG_THREADS = 1024;  // one CTA per row: wide CTAs keep the per-thread chains short when a GPU holds few rows
 enum { C_OUTER = 0, C_NEWTON = 1, C_CG = 2, C_LS = 3 };
 
@@ -436,6 +439,37 @@ __device__ __forceinline__ void logi_set_cond(const GadmmLogi& p, const LogiCond
                                               unsigned int v) {
   p.cond[which] = v;
   if (lc.h[which] != 0) cudaGraphSetConditional(lc.h[which], v);
+}
+
+// A row of the batched solve is handled by a cluster of LG_CL CTAs, each owning a contiguous slice
+// of the d columns: with few rows per GPU (32 at config 3 on 8 GPUs) one CTA per row would leave
+// most SMs idle and the step would be bound by one SM's L2 bandwidth per row.
+struct RowSlice {
+  int n, j0, j1;
+  unsigned rank;
+};
+__device__ __forceinline__ RowSlice logi_slice(int d) {
+  RowSlice r;
+  r.n = blockIdx.x / LG_CL;
+  r.rank = blockIdx.x % LG_CL;
+  const int per = (d + LG_CL - 1) / LG_CL;
+  r.j0 = (int)r.rank * per;
+  r.j1 = min(d, r.j0 + per);
+  return r;
+}
+// Sum of `v` over all threads of the cluster, identical in every thread (fixed order): block sum,
+// then the LG_CL block sums are read through distributed shared memory.  `slot` = one shared
+// double per call site (distinct call sites use distinct slots, so one cluster barrier each).
+__device__ __forceinline__ double cluster_sum(double v, double* red, double* slot) {
+  namespace cg = cooperative_groups;
+  cg::cluster_group cl = cg::this_cluster();
+  v = block_sum(v, red);
+  if (threadIdx.x == 0) *slot = v;
+  cl.sync();
+  double t = 0.0;
+#pragma unroll
+  for (unsigned r = 0; r < (unsigned)LG_CL; ++r) t += *cl.map_shared_rank(slot, r);
+  return t;
 }
 
 // Ticket: returns true (to every thread) in the last CTA of the grid; `any` is OR-reduced over
@@ -559,16 +593,19 @@ logi_setup_kernel(const GadmmLogi p, const LogiConds lc, const int colour) {
 // in a fixed order (deterministic) together with the regulariser mu q.  The step also keeps the
 // line search's starting point up to date (xtry = x - p for live rows, slope = g'p), so that the
 // line search can start as soon as the CG loop ends, whenever that is.
-__global__ void __launch_bounds__(LG_THREADS)
+__global__ void __cluster_dims__(LG_CL, 1, 1) __launch_bounds__(LG_THREADS)
 logi_cg_step_kernel(const GadmmLogi p, const LogiConds lc, const int colour) {
   __shared__ double red[32];
+  __shared__ double slots[3];
   __shared__ unsigned int s_ticket;
-  const int n = blockIdx.x, tid = threadIdx.x, d = p.d;
+  const int tid = threadIdx.x, d = p.d;
+  const RowSlice rs_ = logi_slice(d);
+  const int n = rs_.n;
   const int G = p.G[colour] > 0 ? p.G[colour] : 1;
   const double* part = p.scratch + (size_t)n * G * d;
-  const double mu = p.mu[n], rs = p.rs[n], t = p.t[n];
+  const double mu = p.mu[n], rs = p.rs[n], t = p.t[n], eta = p.eta[n];
   double qhq = 0.0;
-  for (int j = tid; j < d; j += LG_THREADS) {
+  for (int j = rs_.j0 + tid; j < rs_.j1; j += LG_THREADS) {
     const size_t o = (size_t)n * d + j;
     const double qv = p.q[o];
     double hv = 0.0;
@@ -577,10 +614,10 @@ logi_cg_step_kernel(const GadmmLogi p, const LogiConds lc, const int colour) {
     p.hq[o] = hv;
     qhq = fma(qv, hv, qhq);
   }
-  qhq = block_sum(qhq, red);
+  qhq = cluster_sum(qhq, red, &slots[0]);
   const double alpha = qhq > 0.0 ? rs / qhq : 0.0;
   double rs_new = 0.0, slope = 0.0;
-  for (int j = tid; j < d; j += LG_THREADS) {
+  for (int j = rs_.j0 + tid; j < rs_.j1; j += LG_THREADS) {
     const size_t o = (size_t)n * d + j;
     const double pv = fma(alpha, p.q[o], p.p[o]);
     p.p[o] = pv;
@@ -590,20 +627,21 @@ logi_cg_step_kernel(const GadmmLogi p, const LogiConds lc, const int colour) {
     slope = fma(p.g[o], pv, slope);
     p.xtry[o] = fma(-t, pv, p.x[o]);
   }
-  rs_new = block_sum(rs_new, red);
-  slope = block_sum(slope, red);
+  rs_new = cluster_sum(rs_new, red, &slots[1]);
+  slope = cluster_sum(slope, red, &slots[2]);
   const double beta = rs > 0.0 ? rs_new / rs : 0.0;
-  for (int j = tid; j < d; j += LG_THREADS) {
+  for (int j = rs_.j0 + tid; j < rs_.j1; j += LG_THREADS) {
     const size_t o = (size_t)n * d + j;
     p.q[o] = fma(beta, p.q[o], p.r[o]);
   }
-  if (tid == 0) {
+  if (tid == 0 && rs_.rank == 0) {
     p.rs[n] = rs_new;
     p.slope[n] = slope;
   }
-  const bool more = sqrt(rs_new) > p.eta[n];
+  const bool more = sqrt(rs_new) > eta;
   bool any;
-  if (logi_last_cta(p, 2, more, &s_ticket, &any) && tid == 0) {
+  const bool last = logi_last_cta(p, 2, more, &s_ticket, &any);
+  if (last && tid == 0) {
     const unsigned long long c = p.ctrl[5] + 1ull;
     p.ctrl[5] = c;
     p.ctrl[6] = 0ull;
@@ -611,29 +649,36 @@ logi_cg_step_kernel(const GadmmLogi p, const LogiConds lc, const int colour) {
     logi_set_cond(p, lc, C_LS, 1u);              // the line search evaluates at least once
     logi_set_cond(p, lc, C_CG, (any && c < (unsigned long long)p.max_cg) ? 1u : 0u);
   }
+  cooperative_groups::this_cluster().sync();     // peers may still be reading this CTA's slots
 }
 
 // ---- Armijo test of the trial points (hq = X'w(X xtry), losstry from the pass); rows that fail
 // halve their step and every row is evaluated again, so that the last evaluation is at the
 // accepted points of ALL rows (its data terms and curvature state are reused afterwards).
-__global__ void __launch_bounds__(LG_THREADS)
+__global__ void __cluster_dims__(LG_CL, 1, 1) __launch_bounds__(LG_THREADS)
 logi_ls_step_kernel(const GadmmLogi p, const LogiConds lc, const int colour) {
   __shared__ double red[32];
+  __shared__ double slots[3];
   __shared__ unsigned int s_ticket;
   __shared__ double s_loss;
-  const int n = blockIdx.x, tid = threadIdx.x, d = p.d;
+  const int tid = threadIdx.x, d = p.d, rows = gridDim.x / LG_CL;
+  const RowSlice rs_ = logi_slice(d);
+  const int n = rs_.n;
   const int G = p.G[colour] > 0 ? p.G[colour] : 1;
   const double* part = p.scratch + (size_t)n * G * d;
-  const double mu = p.mu[n];
+  // per-row scalars are read before the first cluster barrier: rank 0 rewrites some of them below
+  const double mu = p.mu[n], f = p.f[n], t = p.t[n], slope0 = p.slope[n];
+  const bool live = p.live[n] != 0;
+  const bool capped = p.ctrl[6] + 1ull >= (unsigned long long)p.max_ls;
   if (tid == 0) {                                // loss of the trial point: G partials, fixed order
-    const double* lp = p.scratch + (size_t)gridDim.x * G * d + (size_t)n * G;
+    const double* lp = p.scratch + (size_t)rows * G * d + (size_t)n * G;
     double l = 0.0;
     for (int g = 0; g < G; ++g) l += __ldcg(lp + g);
-    p.losstry[n] = l;
+    if (rs_.rank == 0) p.losstry[n] = l;
     s_loss = l;
   }
   double s_xx = 0.0, s_lx = 0.0, s_alx = 0.0;
-  for (int j = tid; j < d; j += LG_THREADS) {
+  for (int j = rs_.j0 + tid; j < rs_.j1; j += LG_THREADS) {
     const size_t o = (size_t)n * d + j;
     const double xv = p.xtry[o];
     double v = 0.0;                              // data part of the trial gradient
@@ -644,12 +689,11 @@ logi_ls_step_kernel(const GadmmLogi p, const LogiConds lc, const int colour) {
     s_lx += lx;
     s_alx += fabs(lx);
   }
-  s_xx = block_sum(s_xx, red);
-  s_lx = block_sum(s_lx, red);
-  s_alx = block_sum(s_alx, red);
-  const double loss_try = s_loss;                // (block_sum's barriers make it visible)
+  s_xx = cluster_sum(s_xx, red, &slots[0]);
+  s_lx = cluster_sum(s_lx, red, &slots[1]);
+  s_alx = cluster_sum(s_alx, red, &slots[2]);
+  const double loss_try = s_loss;                // (the barriers above make it visible)
   const double f_try = loss_try + 0.5 * mu * s_xx + s_lx;
-  const double f = p.f[n], t = p.t[n];
   // A predicted decrease below the rounding noise of f cannot be tested: accept it.  f is the sum
   // of three terms that may cancel (loss, quadratic, linear), each accumulated over thousands of
   // products, so the noise is taken relative to their magnitudes, not to |f|.  Without this,
@@ -657,24 +701,25 @@ logi_ls_step_kernel(const GadmmLogi p, const LogiConds lc, const int colour) {
   // shards each, for every row of the colour) on coin-flip Armijo tests.
   const double noise = 256.0 * 2.220446049250313e-16 *
                        (fabs(loss_try) + 0.5 * mu * s_xx + s_alx + 1.0);
-  const bool capped = p.ctrl[6] + 1ull >= (unsigned long long)p.max_ls;
-  const bool bad = p.live[n] && t > 1e-9 && (f_try > f - 1e-4 * t * p.slope[n] + noise) && !capped;
+  const bool bad = live && t > 1e-9 && (f_try > f - 1e-4 * t * slope0 + noise) && !capped;
   if (bad) {
     const double t2 = 0.5 * t;
-    for (int j = tid; j < d; j += LG_THREADS) {
+    for (int j = rs_.j0 + tid; j < rs_.j1; j += LG_THREADS) {
       const size_t o = (size_t)n * d + j;
       p.xtry[o] = fma(-t2, p.p[o], p.x[o]);
     }
-    if (tid == 0) p.t[n] = t2;
+    if (tid == 0 && rs_.rank == 0) p.t[n] = t2;
   }
   // f of the evaluated point; for a failing row it is overwritten by the next trial
-  if (tid == 0) p.eta[n] = f_try;                // eta is free during the line search: holds f_try
+  if (tid == 0 && rs_.rank == 0) p.eta[n] = f_try;   // eta is free during the line search: holds f_try
   bool any;
-  if (logi_last_cta(p, 4, bad, &s_ticket, &any) && tid == 0) {
+  const bool last = logi_last_cta(p, 4, bad, &s_ticket, &any);
+  if (last && tid == 0) {
     p.ctrl[6] += 1ull;
     p.ctrl[9] += 1ull;
     logi_set_cond(p, lc, C_LS, any ? 1u : 0u);
   }
+  cooperative_groups::this_cluster().sync();     // peers may still be reading this CTA's slots
 }
 
 // ---- accept the step: x, f, g at the new point; Newton loop condition
@@ -901,14 +946,14 @@ static void graph_half(Sink& k, const GadmmLogi& p, const LogiPlans& pl, const L
     nw.loop(lc.h[C_CG], &cg);
     if (nw.err == cudaSuccess) {
       emit_hessvec(cg, p, pl, colour);
-      cg.launch(logi_cg_step_kernel, grid, block, 0, p, lc, colour);
+      cg.launch(logi_cg_step_kernel, dim3(rows * LG_CL), block, 0, p, lc, colour);
       if (cg.err != cudaSuccess) nw.err = cg.err;
     }
     Sink ls;
     nw.loop(lc.h[C_LS], &ls);
     if (nw.err == cudaSuccess) {
       emit_eval(ls, p, pl, colour, p.xtry, p.d, p.hq, p.losstry, false);
-      ls.launch(logi_ls_step_kernel, grid, block, 0, p, lc, colour);
+      ls.launch(logi_ls_step_kernel, dim3(rows * LG_CL), block, 0, p, lc, colour);
       if (ls.err != cudaSuccess) nw.err = ls.err;
     }
     nw.launch(logi_newton_next_kernel, grid, block, 0, p, lc, colour);
@@ -1068,14 +1113,14 @@ int gadmm_logi_run_host(const GadmmLogi* p, void* stream) {
         unsigned int cc = 1;
         while (cc) {
           emit_hessvec(k, *p, pl, colour);
-          k.launch(logi_cg_step_kernel, grid, block, 0, *p, lc, colour);
+          k.launch(logi_cg_step_kernel, dim3(rows * LG_CL), block, 0, *p, lc, colour);
           GADMM_CUDA_OK(k.err);
           if (int e = read_cond(*p, C_CG, st, &cc)) return e;
         }
         unsigned int cl = 1;
         while (cl) {
           emit_eval(k, *p, pl, colour, p->xtry, p->d, p->hq, p->losstry, false);
-          k.launch(logi_ls_step_kernel, grid, block, 0, *p, lc, colour);
+          k.launch(logi_ls_step_kernel, dim3(rows * LG_CL), block, 0, *p, lc, colour);
           GADMM_CUDA_OK(k.err);
           if (int e = read_cond(*p, C_LS, st, &cl)) return e;
         }
