@@ -415,6 +415,7 @@ static int xtwx_entry(const void* X, int store, const double* y, const double* x
 // (atomic ticket) which also sets the WHILE condition of the enclosing graph loop.
 // =============================================================================================
 constexpr int LG_CL = 4;      // CTAs (one thread-block cluster) per row in the CG / line-search steps
+                              // when a GPU holds few rows; one CTA per row otherwise
 constexpr int LG_THREADS = 1024;  // one CTA per row: wide CTAs keep the per-thread chains short when a GPU holds few rows
 enum { C_OUTER = 0, C_NEWTON = 1, C_CG = 2, C_LS = 3 };
 
@@ -448,11 +449,12 @@ struct RowSlice {
   int n, j0, j1;
   unsigned rank;
 };
+template <int CL>
 __device__ __forceinline__ RowSlice logi_slice(int d) {
   RowSlice r;
-  r.n = blockIdx.x / LG_CL;
-  r.rank = blockIdx.x % LG_CL;
-  const int per = (d + LG_CL - 1) / LG_CL;
+  r.n = blockIdx.x / CL;
+  r.rank = blockIdx.x % CL;
+  const int per = (d + CL - 1) / CL;
   r.j0 = (int)r.rank * per;
   r.j1 = min(d, r.j0 + per);
   return r;
@@ -460,16 +462,25 @@ __device__ __forceinline__ RowSlice logi_slice(int d) {
 // Sum of `v` over all threads of the cluster, identical in every thread (fixed order): block sum,
 // then the LG_CL block sums are read through distributed shared memory.  `slot` = one shared
 // double per call site (distinct call sites use distinct slots, so one cluster barrier each).
+template <int CL>
 __device__ __forceinline__ double cluster_sum(double v, double* red, double* slot) {
-  namespace cg = cooperative_groups;
-  cg::cluster_group cl = cg::this_cluster();
   v = block_sum(v, red);
-  if (threadIdx.x == 0) *slot = v;
-  cl.sync();
-  double t = 0.0;
+  if constexpr (CL == 1) {
+    return v;
+  } else {
+    namespace cg = cooperative_groups;
+    cg::cluster_group cl = cg::this_cluster();
+    if (threadIdx.x == 0) *slot = v;
+    cl.sync();
+    double t = 0.0;
 #pragma unroll
-  for (unsigned r = 0; r < (unsigned)LG_CL; ++r) t += *cl.map_shared_rank(slot, r);
-  return t;
+    for (unsigned r = 0; r < (unsigned)CL; ++r) t += *cl.map_shared_rank(slot, r);
+    return t;
+  }
+}
+template <int CL>
+__device__ __forceinline__ void cluster_exit() {   // peers may still be reading this CTA's slots
+  if constexpr (CL > 1) cooperative_groups::this_cluster().sync();
 }
 
 // Ticket: returns true (to every thread) in the last CTA of the grid; `any` is OR-reduced over
@@ -593,13 +604,14 @@ logi_setup_kernel(const GadmmLogi p, const LogiConds lc, const int colour) {
 // in a fixed order (deterministic) together with the regulariser mu q.  The step also keeps the
 // line search's starting point up to date (xtry = x - p for live rows, slope = g'p), so that the
 // line search can start as soon as the CG loop ends, whenever that is.
-__global__ void __cluster_dims__(LG_CL, 1, 1) __launch_bounds__(LG_THREADS)
+template <int CL>
+__global__ void __cluster_dims__(CL, 1, 1) __launch_bounds__(LG_THREADS)
 logi_cg_step_kernel(const GadmmLogi p, const LogiConds lc, const int colour) {
   __shared__ double red[32];
   __shared__ double slots[3];
   __shared__ unsigned int s_ticket;
   const int tid = threadIdx.x, d = p.d;
-  const RowSlice rs_ = logi_slice(d);
+  const RowSlice rs_ = logi_slice<CL>(d);
   const int n = rs_.n;
   const int G = p.G[colour] > 0 ? p.G[colour] : 1;
   const double* part = p.scratch + (size_t)n * G * d;
@@ -614,7 +626,7 @@ logi_cg_step_kernel(const GadmmLogi p, const LogiConds lc, const int colour) {
     p.hq[o] = hv;
     qhq = fma(qv, hv, qhq);
   }
-  qhq = cluster_sum(qhq, red, &slots[0]);
+  qhq = cluster_sum<CL>(qhq, red, &slots[0]);
   const double alpha = qhq > 0.0 ? rs / qhq : 0.0;
   double rs_new = 0.0, slope = 0.0;
   for (int j = rs_.j0 + tid; j < rs_.j1; j += LG_THREADS) {
@@ -627,8 +639,8 @@ logi_cg_step_kernel(const GadmmLogi p, const LogiConds lc, const int colour) {
     slope = fma(p.g[o], pv, slope);
     p.xtry[o] = fma(-t, pv, p.x[o]);
   }
-  rs_new = cluster_sum(rs_new, red, &slots[1]);
-  slope = cluster_sum(slope, red, &slots[2]);
+  rs_new = cluster_sum<CL>(rs_new, red, &slots[1]);
+  slope = cluster_sum<CL>(slope, red, &slots[2]);
   const double beta = rs > 0.0 ? rs_new / rs : 0.0;
   for (int j = rs_.j0 + tid; j < rs_.j1; j += LG_THREADS) {
     const size_t o = (size_t)n * d + j;
@@ -649,20 +661,21 @@ logi_cg_step_kernel(const GadmmLogi p, const LogiConds lc, const int colour) {
     logi_set_cond(p, lc, C_LS, 1u);              // the line search evaluates at least once
     logi_set_cond(p, lc, C_CG, (any && c < (unsigned long long)p.max_cg) ? 1u : 0u);
   }
-  cooperative_groups::this_cluster().sync();     // peers may still be reading this CTA's slots
+  cluster_exit<CL>();
 }
 
 // ---- Armijo test of the trial points (hq = X'w(X xtry), losstry from the pass); rows that fail
 // halve their step and every row is evaluated again, so that the last evaluation is at the
 // accepted points of ALL rows (its data terms and curvature state are reused afterwards).
-__global__ void __cluster_dims__(LG_CL, 1, 1) __launch_bounds__(LG_THREADS)
+template <int CL>
+__global__ void __cluster_dims__(CL, 1, 1) __launch_bounds__(LG_THREADS)
 logi_ls_step_kernel(const GadmmLogi p, const LogiConds lc, const int colour) {
   __shared__ double red[32];
   __shared__ double slots[3];
   __shared__ unsigned int s_ticket;
   __shared__ double s_loss;
-  const int tid = threadIdx.x, d = p.d, rows = gridDim.x / LG_CL;
-  const RowSlice rs_ = logi_slice(d);
+  const int tid = threadIdx.x, d = p.d, rows = gridDim.x / CL;
+  const RowSlice rs_ = logi_slice<CL>(d);
   const int n = rs_.n;
   const int G = p.G[colour] > 0 ? p.G[colour] : 1;
   const double* part = p.scratch + (size_t)n * G * d;
@@ -689,9 +702,9 @@ logi_ls_step_kernel(const GadmmLogi p, const LogiConds lc, const int colour) {
     s_lx += lx;
     s_alx += fabs(lx);
   }
-  s_xx = cluster_sum(s_xx, red, &slots[0]);
-  s_lx = cluster_sum(s_lx, red, &slots[1]);
-  s_alx = cluster_sum(s_alx, red, &slots[2]);
+  s_xx = cluster_sum<CL>(s_xx, red, &slots[0]);
+  s_lx = cluster_sum<CL>(s_lx, red, &slots[1]);
+  s_alx = cluster_sum<CL>(s_alx, red, &slots[2]);
   const double loss_try = s_loss;                // (the barriers above make it visible)
   const double f_try = loss_try + 0.5 * mu * s_xx + s_lx;
   // A predicted decrease below the rounding noise of f cannot be tested: accept it.  f is the sum
@@ -719,7 +732,7 @@ logi_ls_step_kernel(const GadmmLogi p, const LogiConds lc, const int colour) {
     p.ctrl[9] += 1ull;
     logi_set_cond(p, lc, C_LS, any ? 1u : 0u);
   }
-  cooperative_groups::this_cluster().sync();     // peers may still be reading this CTA's slots
+  cluster_exit<CL>();
 }
 
 // ---- accept the step: x, f, g at the new point; Newton loop condition
@@ -883,6 +896,9 @@ __global__ void loop_probe_kernel(cudaGraphConditionalHandle h, unsigned int* co
   cudaGraphSetConditional(h, c < n ? 1u : 0u);
 }
 
+// few rows: a cluster of LG_CL CTAs per row keeps the SMs busy; many rows: one CTA per row
+static bool logi_wide(int rows) { return rows * LG_CL <= 148; }   // one wave of 1024-thread CTAs
+
 // -------------------------------------------------------------------------- sequence emitters
 struct LogiPlans {
   XtwxPlan grad, hv;
@@ -946,14 +962,16 @@ static void graph_half(Sink& k, const GadmmLogi& p, const LogiPlans& pl, const L
     nw.loop(lc.h[C_CG], &cg);
     if (nw.err == cudaSuccess) {
       emit_hessvec(cg, p, pl, colour);
-      cg.launch(logi_cg_step_kernel, dim3(rows * LG_CL), block, 0, p, lc, colour);
+      if (logi_wide(rows)) cg.launch(logi_cg_step_kernel<LG_CL>, dim3(rows * LG_CL), block, 0, p, lc, colour);
+      else cg.launch(logi_cg_step_kernel<1>, grid, block, 0, p, lc, colour);
       if (cg.err != cudaSuccess) nw.err = cg.err;
     }
     Sink ls;
     nw.loop(lc.h[C_LS], &ls);
     if (nw.err == cudaSuccess) {
       emit_eval(ls, p, pl, colour, p.xtry, p.d, p.hq, p.losstry, false);
-      ls.launch(logi_ls_step_kernel, dim3(rows * LG_CL), block, 0, p, lc, colour);
+      if (logi_wide(rows)) ls.launch(logi_ls_step_kernel<LG_CL>, dim3(rows * LG_CL), block, 0, p, lc, colour);
+      else ls.launch(logi_ls_step_kernel<1>, grid, block, 0, p, lc, colour);
       if (ls.err != cudaSuccess) nw.err = ls.err;
     }
     nw.launch(logi_newton_next_kernel, grid, block, 0, p, lc, colour);
@@ -1113,14 +1131,16 @@ int gadmm_logi_run_host(const GadmmLogi* p, void* stream) {
         unsigned int cc = 1;
         while (cc) {
           emit_hessvec(k, *p, pl, colour);
-          k.launch(logi_cg_step_kernel, dim3(rows * LG_CL), block, 0, *p, lc, colour);
+          if (logi_wide(rows)) k.launch(logi_cg_step_kernel<LG_CL>, dim3(rows * LG_CL), block, 0, *p, lc, colour);
+          else k.launch(logi_cg_step_kernel<1>, grid, block, 0, *p, lc, colour);
           GADMM_CUDA_OK(k.err);
           if (int e = read_cond(*p, C_CG, st, &cc)) return e;
         }
         unsigned int cl = 1;
         while (cl) {
           emit_eval(k, *p, pl, colour, p->xtry, p->d, p->hq, p->losstry, false);
-          k.launch(logi_ls_step_kernel, dim3(rows * LG_CL), block, 0, *p, lc, colour);
+          if (logi_wide(rows)) k.launch(logi_ls_step_kernel<LG_CL>, dim3(rows * LG_CL), block, 0, *p, lc, colour);
+          else k.launch(logi_ls_step_kernel<1>, grid, block, 0, *p, lc, colour);
           GADMM_CUDA_OK(k.err);
           if (int e = read_cond(*p, C_LS, st, &cl)) return e;
         }
