@@ -6,7 +6,12 @@
 // representable in tf32 and the product is formed as hi*hi' + hi*lo' + lo*hi' (3 MMAs of
 // kind::tf32 into one fp32 TMEM accumulator, error ~2^-21 per product).  To keep the fp32
 // accumulation short, the sample dimension is cut into segments of KSEG samples; each CTA owns
-// one (128x128 output tile, segment) and adds its tile into the fp64 result with RED.ADD.F64.
+// one (128x128 output tile, segment).  The segments of a tile are summed in 64-bit FIXED POINT
+// (integer atomics: exact, hence independent of the order in which the CTAs arrive, so the
+// result is bit-reproducible like every other kernel of the library); the scale is a power of two
+// derived from s * max|x|^2 >= |G_ij|, which leaves > 40 fractional bits against the ~21 good
+// bits of a split-tf32 product.  Only the lower triangle is accumulated; a last kernel converts
+// to fp64, adds into G and mirrors.
 //
 // Data path: a prep kernel writes the (optionally sqrt(w)-scaled) shard transposed and split,
 // Xt_hi / Xt_lo [N][dT][sP] fp32 with samples contiguous (K-major for both MMA operands, since
@@ -14,8 +19,8 @@
 //   warp 0  TMA producer   cp.async.bulk.tensor.3d (box 32 x 128, SWIZZLE_128B) -> 3-stage ring
 //   warp 1  MMA issuer     one elected lane: 4 k-steps x 3 split products per stage,
 //                          tcgen05.commit frees the stage / signals the epilogue; owns TMEM alloc
-//   warps 2-5 epilogue     tcgen05.ld 32x32b (each warp its TMEM lane quarter) -> fp64 atomics,
-//                          mirrored for off-diagonal tiles
+//   warps 2-5 epilogue     tcgen05.ld 32x32b (each warp its TMEM lane quarter) -> fixed-point
+//                          integer atomics on the lower triangle
 // Diagonal tiles load only the A operand (B descriptor aliases it).
 #include "../include/gadmm_b200.h"
 #include "common.cuh"
@@ -44,8 +49,10 @@ __device__ __forceinline__ float tf32_round(float x) {
 template <typename TIn>
 __global__ void __launch_bounds__(256)
 split_transpose_kernel(const TIn* __restrict__ X, const double* __restrict__ w, int s, int d, int sP,
-                       int dT, float* __restrict__ hi, float* __restrict__ lo) {
+                       int dT, float* __restrict__ hi, float* __restrict__ lo,
+                       unsigned int* __restrict__ xmax) {
   __shared__ float tile[32][33];
+  float vmax = 0.f;
   const int n = blockIdx.z, r0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
   const TIn* Xn = X + (size_t)n * s * d;
@@ -58,7 +65,11 @@ split_transpose_kernel(const TIn* __restrict__ X, const double* __restrict__ w, 
       v = (float)x;
     }
     tile[i][tx] = v;
+    vmax = fmaxf(vmax, fabsf(v));
   }
+  // max |x| of matrix n (non-negative floats order like their bit patterns: exact, order-free)
+  for (int o = 16; o > 0; o >>= 1) vmax = fmaxf(vmax, __shfl_xor_sync(0xffffffffu, vmax, o));
+  if (tx == 0 && vmax > 0.f) atomicMax(xmax + n, __float_as_uint(vmax));
   __syncthreads();
   for (int i = ty; i < 32; i += 8) {
     const int c = c0 + i, r = r0 + tx;      // output row = feature c, column = sample r
@@ -70,6 +81,37 @@ split_transpose_kernel(const TIn* __restrict__ X, const double* __restrict__ w, 
       lo[o] = tf32_round(v - h);
     }
   }
+}
+
+// scale[n] = 2^e with s * xmax^2 * 2^e < 2^61: every partial sum of |G_ij| <= s xmax^2 fits.
+__global__ void gram_scale_kernel(const unsigned int* __restrict__ xmax, double* __restrict__ scale,
+                                  int N, int sP) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= N) return;
+  const double xm = (double)__uint_as_float(xmax[n]);
+  const double bound = fmax((double)sP * xm * xm, 1e-300);
+  int e;
+  frexp(bound, &e);                       // bound < 2^e
+  scale[n] = ldexp(1.0, 60 - e);
+}
+
+__device__ __forceinline__ void fixed_add(long long* acc, double val, double scale) {
+  atomicAdd(reinterpret_cast<unsigned long long*>(acc),
+            static_cast<unsigned long long>(__double2ll_rn(val * scale)));
+}
+
+// G (+)= acc / scale on the lower triangle, mirrored; acc is cleared for the next call.
+__global__ void __launch_bounds__(256)
+gram_fixed_finish_kernel(long long* __restrict__ acc, const double* __restrict__ scale,
+                         double* __restrict__ G, int dp) {
+  const int n = blockIdx.z, i = blockIdx.y;
+  const int j = blockIdx.x * 256 + threadIdx.x;
+  if (j > i) return;
+  const size_t o = ((size_t)n * dp + i) * dp + j;
+  const double g = (double)acc[o] / scale[n];
+  acc[o] = 0;
+  G[o] += g;
+  if (j != i) G[((size_t)n * dp + j) * dp + i] += g;
 }
 
 // ------------------------------------------------------------------------------ PTX wrappers
@@ -136,7 +178,7 @@ constexpr uint32_t kIdescTf32 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)
 __global__ void __launch_bounds__(GTHREADS, 1)
 gram_tcgen05_kernel(const __grid_constant__ CUtensorMap map_hi,
                     const __grid_constant__ CUtensorMap map_lo, int sP, int kseg, int dp,
-                    double* __restrict__ G) {
+                    long long* __restrict__ acc, const double* __restrict__ scale) {
   extern __shared__ unsigned char gsm_raw[];
   unsigned char* base =
       reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(gsm_raw) + 1023) & ~uintptr_t(1023));
@@ -218,7 +260,8 @@ gram_tcgen05_kernel(const __grid_constant__ CUtensorMap map_hi,
     mbar_wait(acc_full, 0);
     tc_fence_after();
     const int m = q * 32 + lane;                             // row inside the tile
-    double* Gn = G + (size_t)n * dp * dp;
+    long long* An = acc + (size_t)n * dp * dp;
+    const double sc = scale[n];
     const size_t grow = (size_t)I * GT + m;
     if (nchunks > 0) {
       for (int cb = 0; cb < GT; cb += 32) {
@@ -230,9 +273,7 @@ gram_tcgen05_kernel(const __grid_constant__ CUtensorMap map_hi,
             const size_t gcol = (size_t)J * GT + cb + j;
             if (gcol >= (size_t)dp) continue;
             if (diag && gcol > grow) continue;               // lower triangle of diagonal tiles
-            const double val = (double)__uint_as_float(v[j]);
-            atomicAdd(Gn + grow * dp + gcol, val);
-            if (gcol != grow) atomicAdd(Gn + gcol * dp + grow, val);
+            fixed_add(An + grow * dp + gcol, (double)__uint_as_float(v[j]), sc);
           }
         }
       }
@@ -306,7 +347,7 @@ __device__ __forceinline__ void tc_mma_tf32_pair(uint32_t tmem_d, uint64_t adesc
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GTHREADS, 1)
 gram_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap map_hi,
                          const __grid_constant__ CUtensorMap map_lo, int sP, int kseg, int dp,
-                         double* __restrict__ G) {
+                         long long* __restrict__ acc, const double* __restrict__ scale) {
   extern __shared__ unsigned char gsm_raw[];
   unsigned char* base =
       reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(gsm_raw) + 1023) & ~uintptr_t(1023));
@@ -399,7 +440,8 @@ gram_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap map_hi,
     mbar_wait(acc_full, 0);
     tc_fence_after();
     const int m = q * 32 + lane;
-    double* Gn = G + (size_t)n * dp * dp;
+    long long* An = acc + (size_t)n * dp * dp;
+    const double sc = scale[n];
     const size_t grow = (size_t)arow + m;
     if (nchunks > 0) {
       for (int cb = 0; cb < GT2; cb += 32) {
@@ -419,9 +461,8 @@ gram_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap map_hi,
             const size_t gcol = (size_t)J * GT2 + cb + j;
             if (gcol >= (size_t)dp) continue;
             if (diag && gcol > grow) continue;
-            const double val = (double)__uint_as_float(v[j]) + (double)__uint_as_float(v2[j]);
-            atomicAdd(Gn + grow * dp + gcol, val);
-            if (gcol != grow) atomicAdd(Gn + gcol * dp + grow, val);
+            fixed_add(An + grow * dp + gcol,
+                      (double)__uint_as_float(v[j]) + (double)__uint_as_float(v2[j]), sc);
           }
         }
       }
@@ -469,9 +510,11 @@ using namespace gadmm;
 
 extern "C" {
 
+/* split operands (2 x N x dT x sP floats) + fixed-point accumulators (N x dp x dp int64, dp <= dT)
+ * + per-matrix max|x| and scale */
 size_t gadmm_gram_tc_workspace_floats(int N, int s, int d) {
   const size_t dT = (size_t)(d + GT - 1) / GT * GT, sP = (size_t)(s + GBK - 1) / GBK * GBK;
-  return 2 * (size_t)N * dT * sP;
+  return 2 * (size_t)N * dT * sP + 2 * (size_t)N * dT * dT + 4 * (size_t)N + 64;
 }
 
 int gadmm_gram_tcgen05(const void* X, int x_is_f32, const double* w, int N, int s, int d, int dp,
@@ -484,13 +527,21 @@ int gadmm_gram_tcgen05(const void* X, int x_is_f32, const double* w, int N, int 
   if (const char* e = getenv("GADMM_GRAM_PAIR")) pair = (e[0] == '1');
   if (kseg <= 0) kseg = pair ? 4096 : 2048;      // the pair's epilogue is twice as long: amortise it
   kseg = (kseg + GBK - 1) / GBK * GBK;
+  GADMM_REQUIRE(dp <= dT, "gram_tcgen05: dp=%d exceeds the padded width %d", dp, dT);
   float* hi = work;
   float* lo = work + (size_t)N * dT * sP;
+  // (offsets below keep 16-byte alignment: every term is a multiple of 4 floats)
+  long long* acc = reinterpret_cast<long long*>(lo + (size_t)N * dT * sP);
+  double* scale = reinterpret_cast<double*>(acc + (size_t)N * dT * dT);
+  unsigned int* xmax = reinterpret_cast<unsigned int*>(scale + N);
+  GADMM_CUDA_OK(cudaMemsetAsync(acc, 0, (size_t)N * dp * dp * sizeof(long long), st));
+  GADMM_CUDA_OK(cudaMemsetAsync(xmax, 0, (size_t)N * sizeof(unsigned int), st));
   dim3 pg((sP + 31) / 32, (dT + 31) / 32, N);
   if (x_is_f32)
-    split_transpose_kernel<float><<<pg, 256, 0, st>>>((const float*)X, w, s, d, sP, dT, hi, lo);
+    split_transpose_kernel<float><<<pg, 256, 0, st>>>((const float*)X, w, s, d, sP, dT, hi, lo, xmax);
   else
-    split_transpose_kernel<double><<<pg, 256, 0, st>>>((const double*)X, w, s, d, sP, dT, hi, lo);
+    split_transpose_kernel<double><<<pg, 256, 0, st>>>((const double*)X, w, s, d, sP, dT, hi, lo, xmax);
+  gram_scale_kernel<<<(N + 127) / 128, 128, 0, st>>>(xmax, scale, N, sP);
   GADMM_CUDA_OK(cudaGetLastError());
   if (!accumulate) GADMM_CUDA_OK(cudaMemsetAsync(G, 0, (size_t)N * dp * dp * sizeof(double), st));
   CUtensorMap mh, ml;
@@ -508,12 +559,13 @@ int gadmm_gram_tcgen05(const void* X, int x_is_f32, const double* w, int N, int 
   if (pair) {
     const int nB2 = (dT + GT2 - 1) / GT2;
     dim3 grid(2 * (nB2 * (nB2 + 1) / 2), (sP + kseg - 1) / kseg, N);
-    gram_tcgen05_pair_kernel<<<grid, GTHREADS, GSMEM, st>>>(mh, ml, sP, kseg, dp, G);
+    gram_tcgen05_pair_kernel<<<grid, GTHREADS, GSMEM, st>>>(mh, ml, sP, kseg, dp, acc, scale);
   } else {
     const int nB = dT / GT;
     dim3 grid(nB * (nB + 1) / 2, (sP + kseg - 1) / kseg, N);
-    gram_tcgen05_kernel<<<grid, GTHREADS, GSMEM, st>>>(mh, ml, sP, kseg, dp, G);
+    gram_tcgen05_kernel<<<grid, GTHREADS, GSMEM, st>>>(mh, ml, sP, kseg, dp, acc, scale);
   }
+  gram_fixed_finish_kernel<<<dim3((dp + 255) / 256, dp, N), 256, 0, st>>>(acc, scale, G, dp);
   GADMM_CUDA_OK(cudaGetLastError());
   return 0;
 }

@@ -431,7 +431,8 @@ int gadmm_probe_exchange(double* part, unsigned long long* flag, double* const* 
                          void* stream);
 
 /* ---- tensor-core Gram (K1 proper): G[n] (+)= X_n' diag(w_n) X_n with tcgen05 kind::tf32 in a
- * 3-product hi/lo split (fp32-grade), TMA-fed, TMEM accumulators, fp64 result.  X: [N][s][d] fp64
+ * 3-product hi/lo split (fp32-grade), TMA-fed, TMEM accumulators, fp64 result; K-segments are summed
+ * in 64-bit fixed point (integer atomics), so the result is bit-reproducible.  X: [N][s][d] fp64
  * or fp32; w: optional [N][s] row weights (logistic Hessian X'DX); work: gadmm_gram_tc_workspace_floats
  * floats; kseg: samples per fp32 accumulation segment (0 = 2048). */
 size_t gadmm_gram_tc_workspace_floats(int N, int s, int d);

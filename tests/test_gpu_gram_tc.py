@@ -25,6 +25,9 @@ def test_gram_tc_matches_fp64(N, s, d, dtype):
     assert err < 3e-5, float(err)     # fp32-grade: tf32 split + tensor-core fp32 accumulation
     assert torch.count_nonzero(G[:, d:, :]) == 0 and torch.count_nonzero(G[:, :, d:]) == 0
     torch.testing.assert_close(G, G.transpose(1, 2), rtol=0, atol=0)   # exactly symmetric
+    # K-segments are summed in fixed point (integer atomics): bit-identical run to run
+    for _ in range(2):
+        assert torch.equal(G, LA.gram_tc(X))
 
 
 def test_gram_tc_weighted_and_accumulate():
