@@ -69,8 +69,14 @@ split_transpose_kernel(const TIn* __restrict__ X, const double* __restrict__ w, 
   }
   // max |x| of matrix n (non-negative floats order like their bit patterns: exact, order-free)
   for (int o = 16; o > 0; o >>= 1) vmax = fmaxf(vmax, __shfl_xor_sync(0xffffffffu, vmax, o));
-  if (tx == 0 && vmax > 0.f) atomicMax(xmax + n, __float_as_uint(vmax));
+  __shared__ float wmax[8];
+  if (tx == 0) wmax[ty] = vmax;
   __syncthreads();
+  if (threadIdx.x == 0) {                  // one atomic per block, and only if it can raise the max
+    for (int q = 1; q < 8; ++q) vmax = fmaxf(vmax, wmax[q]);
+    const unsigned int bits = __float_as_uint(vmax);
+    if (bits > *reinterpret_cast<volatile unsigned int*>(xmax + n)) atomicMax(xmax + n, bits);
+  }
   for (int i = ty; i < 32; i += 8) {
     const int c = c0 + i, r = r0 + tx;      // output row = feature c, column = sample r
     if (c < dT && r < sP) {
@@ -100,18 +106,32 @@ __device__ __forceinline__ void fixed_add(long long* acc, double val, double sca
             static_cast<unsigned long long>(__double2ll_rn(val * scale)));
 }
 
-// G (+)= acc / scale on the lower triangle, mirrored; acc is cleared for the next call.
+// G (+)= acc / scale: 32x32 tiles of the lower triangle; the mirror image goes through a shared
+// memory transpose so that both the lower and the upper tile are updated with coalesced rows.
 __global__ void __launch_bounds__(256)
-gram_fixed_finish_kernel(long long* __restrict__ acc, const double* __restrict__ scale,
+gram_fixed_finish_kernel(const long long* __restrict__ acc, const double* __restrict__ scale,
                          double* __restrict__ G, int dp) {
-  const int n = blockIdx.z, i = blockIdx.y;
-  const int j = blockIdx.x * 256 + threadIdx.x;
-  if (j > i) return;
-  const size_t o = ((size_t)n * dp + i) * dp + j;
-  const double g = (double)acc[o] / scale[n];
-  acc[o] = 0;
-  G[o] += g;
-  if (j != i) G[((size_t)n * dp + j) * dp + i] += g;
+  __shared__ double tile[32][33];
+  const int n = blockIdx.z, ti = blockIdx.y, tj = blockIdx.x;
+  if (tj > ti) return;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const double inv = 1.0 / scale[n];                        // power of two: exact
+  const long long* An = acc + (size_t)n * dp * dp;
+  double* Gn = G + (size_t)n * dp * dp;
+  for (int r = ty; r < 32; r += 8) {
+    const int i = ti * 32 + r, j = tj * 32 + tx;
+    double g = 0.0;
+    if (i < dp && j < dp && j <= i) {
+      g = (double)An[(size_t)i * dp + j] * inv;
+      Gn[(size_t)i * dp + j] += g;
+    }
+    tile[r][tx] = g;
+  }
+  __syncthreads();
+  for (int r = ty; r < 32; r += 8) {                        // upper image: element (j, i) = (i, j)
+    const int j = tj * 32 + r, i = ti * 32 + tx;
+    if (i < dp && j < dp && j < i) Gn[(size_t)j * dp + i] += tile[tx][r];
+  }
 }
 
 // ------------------------------------------------------------------------------ PTX wrappers
@@ -178,7 +198,8 @@ constexpr uint32_t kIdescTf32 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)
 __global__ void __launch_bounds__(GTHREADS, 1)
 gram_tcgen05_kernel(const __grid_constant__ CUtensorMap map_hi,
                     const __grid_constant__ CUtensorMap map_lo, int sP, int kseg, int dp,
-                    long long* __restrict__ acc, const double* __restrict__ scale) {
+                    long long* __restrict__ acc, const double* __restrict__ scale,
+                    double* __restrict__ G) {
   extern __shared__ unsigned char gsm_raw[];
   unsigned char* base =
       reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(gsm_raw) + 1023) & ~uintptr_t(1023));
@@ -260,8 +281,12 @@ gram_tcgen05_kernel(const __grid_constant__ CUtensorMap map_hi,
     mbar_wait(acc_full, 0);
     tc_fence_after();
     const int m = q * 32 + lane;                             // row inside the tile
+    // One K segment: this CTA is the only writer of its tile, so fp64 reductions straight into G
+    // (and its mirror image) are already order-free.  Several segments: fixed point.
+    const bool direct = gridDim.y == 1;
     long long* An = acc + (size_t)n * dp * dp;
-    const double sc = scale[n];
+    double* Gn = G + (size_t)n * dp * dp;
+    const double sc = direct ? 1.0 : scale[n];
     const size_t grow = (size_t)I * GT + m;
     if (nchunks > 0) {
       for (int cb = 0; cb < GT; cb += 32) {
@@ -273,7 +298,13 @@ gram_tcgen05_kernel(const __grid_constant__ CUtensorMap map_hi,
             const size_t gcol = (size_t)J * GT + cb + j;
             if (gcol >= (size_t)dp) continue;
             if (diag && gcol > grow) continue;               // lower triangle of diagonal tiles
-            fixed_add(An + grow * dp + gcol, (double)__uint_as_float(v[j]), sc);
+            const double val = (double)__uint_as_float(v[j]);
+            if (direct) {            // single writer per element: the reduction is a plain add
+              atomicAdd(Gn + grow * dp + gcol, val);        // (RED: fire-and-forget, no read stall)
+              if (gcol != grow) atomicAdd(Gn + gcol * dp + grow, val);
+            } else {
+              fixed_add(An + grow * dp + gcol, val, sc);
+            }
           }
         }
       }
@@ -347,7 +378,8 @@ __device__ __forceinline__ void tc_mma_tf32_pair(uint32_t tmem_d, uint64_t adesc
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GTHREADS, 1)
 gram_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap map_hi,
                          const __grid_constant__ CUtensorMap map_lo, int sP, int kseg, int dp,
-                         long long* __restrict__ acc, const double* __restrict__ scale) {
+                         long long* __restrict__ acc, const double* __restrict__ scale,
+                         double* __restrict__ G) {
   extern __shared__ unsigned char gsm_raw[];
   unsigned char* base =
       reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(gsm_raw) + 1023) & ~uintptr_t(1023));
@@ -440,8 +472,10 @@ gram_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap map_hi,
     mbar_wait(acc_full, 0);
     tc_fence_after();
     const int m = q * 32 + lane;
+    const bool direct = gridDim.y == 1;
     long long* An = acc + (size_t)n * dp * dp;
-    const double sc = scale[n];
+    double* Gn = G + (size_t)n * dp * dp;
+    const double sc = direct ? 1.0 : scale[n];
     const size_t grow = (size_t)arow + m;
     if (nchunks > 0) {
       for (int cb = 0; cb < GT2; cb += 32) {
@@ -461,8 +495,13 @@ gram_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap map_hi,
             const size_t gcol = (size_t)J * GT2 + cb + j;
             if (gcol >= (size_t)dp) continue;
             if (diag && gcol > grow) continue;
-            fixed_add(An + grow * dp + gcol,
-                      (double)__uint_as_float(v[j]) + (double)__uint_as_float(v2[j]), sc);
+            const double val = (double)__uint_as_float(v[j]) + (double)__uint_as_float(v2[j]);
+            if (direct) {            // single writer per element: the reduction is a plain add
+              atomicAdd(Gn + grow * dp + gcol, val);        // (RED: fire-and-forget, no read stall)
+              if (gcol != grow) atomicAdd(Gn + gcol * dp + grow, val);
+            } else {
+              fixed_add(An + grow * dp + gcol, val, sc);
+            }
           }
         }
       }
@@ -522,11 +561,7 @@ int gadmm_gram_tcgen05(const void* X, int x_is_f32, const double* w, int N, int 
   GADMM_REQUIRE(N > 0 && s > 0 && d > 0 && dp >= d && dp % 64 == 0, "gram_tcgen05: bad shape");
   cudaStream_t st = (cudaStream_t)stream;
   const int dT = (d + GT - 1) / GT * GT, sP = (s + GBK - 1) / GBK * GBK;
-  // CTA pairs on 256x256 tiles once there are enough of them; GADMM_GRAM_PAIR=0/1 forces a path
-  bool pair = dT >= 512;
-  if (const char* e = getenv("GADMM_GRAM_PAIR")) pair = (e[0] == '1');
-  if (kseg <= 0) kseg = pair ? 4096 : 2048;      // the pair's epilogue is twice as long: amortise it
-  kseg = (kseg + GBK - 1) / GBK * GBK;
+  // (CTA pairs on 256x256 tiles once there are enough of them; GADMM_GRAM_PAIR=0/1 forces a path)
   GADMM_REQUIRE(dp <= dT, "gram_tcgen05: dp=%d exceeds the padded width %d", dp, dT);
   float* hi = work;
   float* lo = work + (size_t)N * dT * sP;
@@ -534,7 +569,12 @@ int gadmm_gram_tcgen05(const void* X, int x_is_f32, const double* w, int N, int 
   long long* acc = reinterpret_cast<long long*>(lo + (size_t)N * dT * sP);
   double* scale = reinterpret_cast<double*>(acc + (size_t)N * dT * dT);
   unsigned int* xmax = reinterpret_cast<unsigned int*>(scale + N);
-  GADMM_CUDA_OK(cudaMemsetAsync(acc, 0, (size_t)N * dp * dp * sizeof(long long), st));
+  bool pair = dT >= 512;
+  if (const char* e = getenv("GADMM_GRAM_PAIR")) pair = (e[0] == '1');
+  if (kseg <= 0) kseg = pair ? 4096 : 2048;      // the pair's epilogue is twice as long: amortise it
+  kseg = (kseg + GBK - 1) / GBK * GBK;
+  const int nseg = (sP + kseg - 1) / kseg;
+  if (nseg > 1) GADMM_CUDA_OK(cudaMemsetAsync(acc, 0, (size_t)N * dp * dp * sizeof(long long), st));
   GADMM_CUDA_OK(cudaMemsetAsync(xmax, 0, (size_t)N * sizeof(unsigned int), st));
   dim3 pg((sP + 31) / 32, (dT + 31) / 32, N);
   if (x_is_f32)
@@ -558,14 +598,15 @@ int gadmm_gram_tcgen05(const void* X, int x_is_f32, const double* w, int N, int 
   }
   if (pair) {
     const int nB2 = (dT + GT2 - 1) / GT2;
-    dim3 grid(2 * (nB2 * (nB2 + 1) / 2), (sP + kseg - 1) / kseg, N);
-    gram_tcgen05_pair_kernel<<<grid, GTHREADS, GSMEM, st>>>(mh, ml, sP, kseg, dp, acc, scale);
+    dim3 grid(2 * (nB2 * (nB2 + 1) / 2), nseg, N);
+    gram_tcgen05_pair_kernel<<<grid, GTHREADS, GSMEM, st>>>(mh, ml, sP, kseg, dp, acc, scale, G);
   } else {
     const int nB = dT / GT;
-    dim3 grid(nB * (nB + 1) / 2, (sP + kseg - 1) / kseg, N);
-    gram_tcgen05_kernel<<<grid, GTHREADS, GSMEM, st>>>(mh, ml, sP, kseg, dp, acc, scale);
+    dim3 grid(nB * (nB + 1) / 2, nseg, N);
+    gram_tcgen05_kernel<<<grid, GTHREADS, GSMEM, st>>>(mh, ml, sP, kseg, dp, acc, scale, G);
   }
-  gram_fixed_finish_kernel<<<dim3((dp + 255) / 256, dp, N), 256, 0, st>>>(acc, scale, G, dp);
+  if (nseg > 1)
+    gram_fixed_finish_kernel<<<dim3((dp + 31) / 32, (dp + 31) / 32, N), 256, 0, st>>>(acc, scale, G, dp);
   GADMM_CUDA_OK(cudaGetLastError());
   return 0;
 }
