@@ -166,36 +166,43 @@ __global__ void shift_copy_kernel(const double* __restrict__ G, double* __restri
 
 // ------------------------------------------------------------------------ blocked Cholesky
 // Diagonal block k: L_kk = chol(A_kk) in place (upper zeroed) and Dinv[n][k] = L_kk^-1.
-__global__ void __launch_bounds__(64)
+// 256 threads: t = row, q = one of four column groups of the trailing update (this kernel sits on
+// the critical path of every block column, so its latency matters more than its flops).
+__global__ void __launch_bounds__(256)
 potrf_diag_kernel(double* __restrict__ A, double* __restrict__ Dinv, int dp, int nT, int k) {
   extern __shared__ __align__(16) unsigned char dsm[];
   double (*L)[B + 1] = reinterpret_cast<double (*)[B + 1]>(dsm);
   double (*Li)[B + 1] = L + B;
-  const int n = blockIdx.x, t = threadIdx.x;
+  const int n = blockIdx.x, t = threadIdx.x & 63, q = threadIdx.x >> 6;
   double* Ak = A + (size_t)n * dp * dp + (size_t)k * B * dp + (size_t)k * B;
-  for (int r = 0; r < B; ++r) L[r][t] = Ak[(size_t)r * dp + t];
+  for (int r = q; r < B; r += 4) {
+    L[r][t] = Ak[(size_t)r * dp + t];
+    Li[r][t] = 0.0;
+  }
   __syncthreads();
   for (int j = 0; j < B; ++j) {
-    if (t == j) L[j][j] = sqrt(L[j][j]);
+    if (threadIdx.x == 0) L[j][j] = sqrt(L[j][j]);
     __syncthreads();
-    if (t > j) L[t][j] /= L[j][j];
+    if (q == 0 && t > j) L[t][j] /= L[j][j];
     __syncthreads();
-    // rank-1 update of the trailing lower part: row t, columns j+1..t
-    if (t > j)
-      for (int cc = j + 1; cc <= t; ++cc) L[t][cc] = fma(-L[t][j], L[cc][j], L[t][cc]);
+    // rank-1 update of the trailing lower part: row t, columns j+1..t, split over the 4 groups
+    if (t > j) {
+      const double ltj = L[t][j];
+      for (int cc = j + 1 + q; cc <= t; cc += 4) L[t][cc] = fma(-ltj, L[cc][j], L[t][cc]);
+    }
     __syncthreads();
   }
-  // inverse of the lower-triangular block: thread t solves L x = e_t
-  for (int r = 0; r < B; ++r) Li[r][t] = 0.0;
-  __syncthreads();
-  for (int r = t; r < B; ++r) {
-    double v = (r == t) ? 1.0 : 0.0;
-    for (int m = t; m < r; ++m) v = fma(-L[r][m], Li[m][t], v);
-    Li[r][t] = v / L[r][r];
+  // inverse of the lower-triangular block: thread t (group 0) solves L x = e_t
+  if (q == 0) {
+    for (int r = t; r < B; ++r) {
+      double v = (r == t) ? 1.0 : 0.0;
+      for (int m = t; m < r; ++m) v = fma(-L[r][m], Li[m][t], v);
+      Li[r][t] = v / L[r][r];
+    }
   }
   __syncthreads();
   double* Dk = Dinv + ((size_t)n * nT + k) * B * B;
-  for (int r = 0; r < B; ++r) {
+  for (int r = q; r < B; r += 4) {
     Ak[(size_t)r * dp + t] = (t <= r) ? L[r][t] : 0.0;
     Dk[r * B + t] = Li[r][t];
   }
@@ -363,7 +370,7 @@ int gadmm_spd_inverse_f64(double* A, double* W, double* Dinv, int N, int dp, voi
   GADMM_CUDA_OK(cudaFuncSetAttribute(lauum_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kBlkSmem));
   for (int k = 0; k < nT; ++k) {       // left-looking: bring column k up to date, factor, solve
     if (k > 0) chol_update_kernel<<<dim3(nT - k, N), 256, kBlkSmem, st>>>(A, dp, nT, k);
-    potrf_diag_kernel<<<N, 64, kDiagSmem, st>>>(A, Dinv, dp, nT, k);
+    potrf_diag_kernel<<<N, 256, kDiagSmem, st>>>(A, Dinv, dp, nT, k);
     const int rest = nT - k - 1;
     if (rest > 0) panel_kernel<<<dim3(rest, N), 256, kBlkSmem, st>>>(A, Dinv, dp, nT, k);
   }
