@@ -287,3 +287,155 @@ def test_dgadmm_rechain_without_the_exchange_is_caught():
     exchange stays on every iteration of a re-chained run."""
     _, bad = _explore_dgadmm(_CHAINS4, 4, with_exchange=False)
     assert bad is not None and bad[0] != "deadlock" and bad[4] == -1
+
+
+# ------------------------------------------------------------------------------------------------
+# Round 2: whole windows run under programmatic dependent launch, so a worker's SOLVE (streaming
+# kernel + finisher) and its DUAL UPDATE (gadmm_dual_objective_kernel) are different CTAs of
+# different, overlapping kernels.  They are ordered only by data: the solve of iteration it waits
+# for nuflag[w] >= it-1 (csrc/gadmm_iter.cu: wait_flag_ge_gpu(c.nuflag + k, it - 1)), the dual update
+# of iteration it waits for the version flags of w and of its neighbours >= it.  Model: two
+# asynchronous processes per worker, every interleaving explored.
+def _explore_split(n_workers: int, n_iter: int, use_nuflag: bool = True):
+    colour = [w % 2 for w in range(n_workers)]
+    nbrs = [[v for v in (w - 1, w + 1) if 0 <= v < n_workers] for w in range(n_workers)]
+    init = (tuple((1, 0) for _ in range(n_workers)),            # solver  (it, pc)
+            tuple((1, 0) for _ in range(n_workers)),            # dual    (it, pc)
+            tuple((0, 0) for _ in range(n_workers)),            # theta slots (versions)
+            tuple(0 for _ in range(n_workers)),                 # version flags
+            tuple(0 for _ in range(n_workers)),                 # nu version (-1 = torn)
+            tuple(0 for _ in range(n_workers)))                 # nuflag
+    seen = {init}
+    stack = [init]
+    while stack:
+        S, D, mem, flags, nu, nuflag = stack.pop()
+        moved = False
+        for w in range(n_workers):
+            k = len(nbrs[w])
+            # ---------------- solver process
+            it, pc = S[w]
+            if it <= n_iter:
+                need = it - 1 if colour[w] == 0 else it
+                nS, nmem, nflags = None, mem, flags
+                if pc == 0:                                   # own dual of iteration it-1
+                    if not use_nuflag or nuflag[w] >= it - 1:
+                        if nu[w] != it - 1:
+                            return len(seen), ("nu", w, it, nu[w])
+                        nS = (it, 1)
+                elif pc <= k:
+                    v = nbrs[w][pc - 1]
+                    if flags[v] >= need:
+                        if mem[v][need % 2] != need:
+                            return len(seen), ("theta-solve", w, it, v, mem[v][need % 2])
+                        nS = (it, pc + 1)
+                elif pc == k + 1:
+                    row = list(mem[w]); row[it % 2] = -1
+                    nmem = mem[:w] + (tuple(row),) + mem[w + 1:]
+                    nS = (it, pc + 1)
+                elif pc == k + 2:
+                    row = list(mem[w]); row[it % 2] = it
+                    nmem = mem[:w] + (tuple(row),) + mem[w + 1:]
+                    nS = (it, pc + 1)
+                else:
+                    nflags = flags[:w] + (it,) + flags[w + 1:]
+                    nS = (it + 1, 0)
+                if nS is not None:
+                    moved = True
+                    st = (S[:w] + (nS,) + S[w + 1:], D, nmem, nflags, nu, nuflag)
+                    if st not in seen:
+                        seen.add(st); stack.append(st)
+            # ---------------- dual process
+            it, pc = D[w]
+            if it <= n_iter:
+                readers = [w] + nbrs[w]
+                nD, nnu, nnf = None, nu, nuflag
+                if pc < len(readers):
+                    v = readers[pc]
+                    if flags[v] >= it:
+                        if mem[v][it % 2] != it:
+                            return len(seen), ("theta-dual", w, it, v, mem[v][it % 2])
+                        nD = (it, pc + 1)
+                elif pc == len(readers):
+                    nnu = nu[:w] + (-1,) + nu[w + 1:]
+                    nD = (it, pc + 1)
+                elif pc == len(readers) + 1:
+                    nnu = nu[:w] + (it,) + nu[w + 1:]
+                    nD = (it, pc + 1)
+                else:
+                    nnf = nuflag[:w] + (it,) + nuflag[w + 1:]
+                    nD = (it + 1, 0)
+                if nD is not None:
+                    moved = True
+                    st = (S, D[:w] + (nD,) + D[w + 1:], mem, flags, nnu, nnf)
+                    if st not in seen:
+                        seen.add(st); stack.append(st)
+        if not moved and (any(i <= n_iter for i, _ in S) or any(i <= n_iter for i, _ in D)):
+            return len(seen), ("deadlock", S, D, flags, nuflag)
+    return len(seen), None
+
+
+@pytest.mark.parametrize("n_workers,n_iter", [(2, 4), (3, 3)])
+def test_window_protocol_solver_and_dual_as_separate_processes(n_workers, n_iter):
+    states, bad = _explore_split(n_workers, n_iter, use_nuflag=True)
+    assert bad is None, bad
+    assert states > 100
+
+
+def test_window_protocol_without_the_dual_flag_is_caught():
+    """Negative control: if the next solve did not wait for nuflag, it could assemble its right-hand
+    side from a node dual that is stale or half written."""
+    _, bad = _explore_split(2, 3, use_nuflag=False)
+    assert bad is not None and bad[0] == "nu"
+
+
+# ------------------------------------------------------------------------------------------------
+# DGD across GPUs (csrc/first_order.cu: own_exchange_kernel / dgd_update_kernel): the neighbour's
+# boundary gradient row lands in a SINGLE-buffered halo row.  Per iteration a rank (one stream, in
+# order): posts its objective partial fx(it); pushes its boundary row (version it) into the
+# neighbour; update(it) waits for the neighbour's row flag >= it and reads the halo.  The push of
+# iteration it waits for the neighbour's fx post of iteration it (back-pressure): that post comes
+# after the neighbour's update(it-1) in its stream, so the halo row of it-1 has been consumed.
+def _explore_dgd(n_iter: int, backpressure: bool):
+    # two ranks; state per rank: (it, pc); halo[r] = version of the row that rank r RECEIVED
+    init = (((1, 0), (1, 0)), (0, 0), (0, 0), (0, 0))       # procs, halo, rowflag, fxpost
+    seen = {init}
+    stack = [init]
+    while stack:
+        procs, halo, rowflag, fx = stack.pop()
+        moved = False
+        for r in (0, 1):
+            o = 1 - r
+            it, pc = procs[r]
+            if it > n_iter:
+                continue
+            nh, nrf, nfx, nxt = halo, rowflag, fx, None
+            if pc == 0:                                    # post fx(it)
+                nfx = tuple(it if q == r else fx[q] for q in (0, 1))
+                nxt = (it, 1)
+            elif pc == 1:                                  # push own row into the peer's halo
+                if not backpressure or fx[o] >= it:
+                    nh = tuple(it if q == o else halo[q] for q in (0, 1))
+                    nxt = (it, 2)
+            elif pc == 2:                                  # release the row flag at the peer
+                nrf = tuple(it if q == o else rowflag[q] for q in (0, 1))
+                nxt = (it, 3)
+            else:                                          # update(it): wait for the row, read it
+                if rowflag[r] >= it:
+                    if halo[r] != it:
+                        return len(seen), (r, it, halo[r])
+                    nxt = (it + 1, 0)
+            if nxt is not None:
+                moved = True
+                st = (tuple(nxt if q == r else procs[q] for q in (0, 1)), nh, nrf, nfx)
+                if st not in seen:
+                    seen.add(st); stack.append(st)
+        if not moved and any(i <= n_iter for i, _ in procs):
+            return len(seen), ("deadlock", procs)
+    return len(seen), None
+
+
+def test_dgd_halo_with_backpressure_is_safe_and_without_is_caught():
+    _, bad = _explore_dgd(5, backpressure=True)
+    assert bad is None, bad
+    _, bad = _explore_dgd(5, backpressure=False)
+    assert bad is not None and bad[0] != "deadlock"       # reads the row of iteration it+1
