@@ -78,32 +78,26 @@ class _Backend:
         return star_admm(XX, YY, rho, N, d, s, num_iter, obj0, acc, backend=self.name)
 
 
-    # first-order baselines: workers split over the ranks, all_gather / all_reduce only
-    def gd_dgd_lag(self, *a, **kw):
-        from .dist_first_order import gd_dgd_lag
-        return gd_dgd_lag(*a, backend=self.name, **kw)
+    # Families that live in their own modules (first-order baselines: workers split over the ranks,
+    # all_gather / all_reduce only; logistic GADMM: per-rank local solves, all_gather of the model
+    # matrix per colour): resolved by name on first use, called with this backend.
+    _LAZY = {
+        "gd_dgd_lag": ("dist_first_order", "gd_dgd_lag"),
+        "gd_dgd_lag_logistic": ("dist_first_order", "gd_dgd_lag_logistic"),
+        "dual_averaging": ("dist_first_order", "dual_averaging"),
+        "dual_averaging_logistic": ("dist_first_order", "dual_averaging_logistic"),
+        "gadmm_logistic": ("dist_logistic", "group_admm_logistic"),
+        "gadmm_logistic_gd": ("dist_logistic", "group_admm_logistic_gd"),
+    }
 
-    def gd_dgd_lag_logistic(self, *a, **kw):
-        from .dist_first_order import gd_dgd_lag_logistic
-        return gd_dgd_lag_logistic(*a, backend=self.name, **kw)
-
-    def dual_averaging(self, *a, **kw):
-        from .dist_first_order import dual_averaging
-        return dual_averaging(*a, backend=self.name, **kw)
-
-    def dual_averaging_logistic(self, *a, **kw):
-        from .dist_first_order import dual_averaging_logistic
-        return dual_averaging_logistic(*a, backend=self.name, **kw)
-
-
-    # logistic GADMM: oracle local solvers per rank, all_gather of the model matrix per colour
-    def gadmm_logistic(self, *a, **kw):
-        from .dist_logistic import group_admm_logistic
-        return group_admm_logistic(*a, backend=self.name, **kw)
-
-    def gadmm_logistic_gd(self, *a, **kw):
-        from .dist_logistic import group_admm_logistic_gd
-        return group_admm_logistic_gd(*a, backend=self.name, **kw)
+    def __getattr__(self, name):
+        if name in _Backend._LAZY:
+            import functools
+            import importlib
+            mod, fn = _Backend._LAZY[name]
+            f = getattr(importlib.import_module(f"{__package__}.{mod}"), fn)
+            return functools.partial(f, backend=self.name)
+        raise AttributeError(name)
 
 
 def get(name: str) -> _Backend:
