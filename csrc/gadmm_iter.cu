@@ -364,7 +364,6 @@ gadmm_dual_objective_kernel(const GadmmChain c, const int off) {
     c.obj_hist[it] = total;
     c.loss_hist[it] = loss;
     c.t_hist[it] = globaltimer_ns();
-    if (c.last) { c.last[0] = total; c.last[1] = loss; }
     if (loss < c.acc && c.ctrl[1] == 0ull) c.ctrl[1] = it;
     c.ctrl[0] = it + 1ull;
     __threadfence();

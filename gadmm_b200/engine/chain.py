@@ -107,7 +107,6 @@ class ChainEngine:
         self.counters = torch.zeros((Nloc + 2,), dtype=i32, device=dev)
         self.objw = torch.zeros((2, Nloc), dtype=f64, device=dev)
         self.sync = torch.zeros((2,), dtype=i64, device=dev)       # window base, decided-through
-        self.last = torch.zeros((2,), dtype=f64, device=dev)       # (obj, loss) of the last iteration
         self.nuflag = torch.zeros((Nloc,), dtype=i64, device=dev)
         # parallel finisher (csrc/gadmm_iter.cu: gadmm_finish_kernel) for d >= 512
         self.split_finish = (dp // 64 >= 8) and os.environ.get("GADMM_B200_NO_SPLIT") != "1"
@@ -322,7 +321,6 @@ class ChainEngine:
         c.nsplit = int(self.nsplit)
         c.order = self.order.data_ptr()
         c.sync, c.nuflag = self.sync.data_ptr(), self.nuflag.data_ptr()
-        c.last = self.last.data_ptr()
         c.wready, c.sblk, c.fin_counters = (self.wready.data_ptr(), self.sblk.data_ptr(),
                                             self.fin_counters.data_ptr())
         self._desc = c
@@ -511,40 +509,25 @@ class ChainEngine:
     def step(self, path0=None):
         """One GADMM iteration driven from the host, end to end: the step's control block (chain
         tables + inverse pointer table; a new chain if ``path0`` is given) is copied host->device
-        from pinned memory, the kernels run, and ``(objective, loss)`` of the iteration is read
-        back device->host.  This is the user-facing online mode (e.g. D-GADMM where an external
-        radio layer supplies the chain every step).  The four pieces -- two H2D copies, the
-        iteration's kernels, one D2H copy -- are captured once as a CUDA graph (fixed pinned and
-        device addresses; the kernels take the iteration from the device counter), so a step costs
-        one graph launch and one stream synchronisation.  Returns ``(obj, loss)``."""
+        from pinned memory, the three kernels run, and ``(objective, loss)`` of the iteration is
+        read back device->host.  This is the user-facing online mode (e.g. D-GADMM where an
+        external radio layer supplies the chain every step).  Returns ``(obj, loss)``."""
         if not hasattr(self, "_step_out"):
             self._step_out = torch.zeros((2,), dtype=torch.float64).pin_memory()
             nv.lib().gadmm_chain_configure()
-            self._step_graph = None
+            self._it_host = int(self.ctrl[0].item())
         if path0 is not None:
-            self.set_path(path0)                 # rewrites the pinned tables (and uploads them)
-        if self._step_graph is None and os.environ.get("GADMM_B200_NO_STEP_GRAPH") != "1":
-            self._step_body()                    # warm-up outside capture
-            torch.cuda.current_stream().synchronize()
-            out = (float(self._step_out[0]), float(self._step_out[1]))
-            g = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(g):
-                self._step_body()
-            self._step_graph = g
-            return out
-        if self._step_graph is not None:
-            self._step_graph.replay()
-            self.launches += (5 if self.split_finish else 3) + 1
+            self.set_path(path0)
         else:
-            self._step_body()
-        torch.cuda.current_stream().synchronize()
-        return float(self._step_out[0]), float(self._step_out[1])
-
-    def _step_body(self):
-        self.tab.copy_(self.tab_host, non_blocking=True)
-        self.Mptr.copy_(self.Mptr_host, non_blocking=True)
+            self.tab.copy_(self.tab_host, non_blocking=True)
+            self.Mptr.copy_(self.Mptr_host, non_blocking=True)
         self.iterate(1, use_graph=False)
-        self._step_out.copy_(self.last, non_blocking=True)
+        it = self._it_host
+        self._step_out[0:1].copy_(self.obj_hist[it:it + 1], non_blocking=True)
+        self._step_out[1:2].copy_(self.loss_hist[it:it + 1], non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        self._it_host += 1
+        return float(self._step_out[0]), float(self._step_out[1])
 
     @property
     def step_h2d_bytes(self) -> int:
@@ -677,7 +660,7 @@ class ChainEngine:
         self._resume_from = 0
         self._desc = None
         self._graphs = {}
-        for name in ("_step_out", "_it_host", "_step_graph"):
+        for name in ("_step_out", "_it_host"):
             if hasattr(self, name):
                 delattr(self, name)
         torch.cuda.synchronize(self.dev)

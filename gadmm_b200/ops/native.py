@@ -37,7 +37,7 @@ class GadmmChain(C.Structure):
         ("nranks", C.c_int), ("store", C.c_int), ("max_iter", C.c_int), ("pdl", C.c_int),
         ("split_finish", C.c_int), ("wready", _vp), ("sblk", _vp), ("fin_counters", _vp),
         ("nsplit", C.c_int), ("reserved", C.c_int), ("order", _vp),
-        ("sync", _vp), ("nuflag", _vp), ("last", _vp),
+        ("sync", _vp), ("nuflag", _vp),
     ]
 
 

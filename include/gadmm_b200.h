@@ -127,8 +127,6 @@ typedef struct GadmmChain {
   unsigned long long* sync;  /* [2]: [0] = first iteration of the window being executed, [1] = last
                                 iteration whose stop decision is final (both written on the device) */
   unsigned long long* nuflag; /* [Nloc] iteration through which nu_k has been updated */
-  double* last;              /* optional [2]: (objective, loss) of the most recent iteration, for a
-                                fixed-address device->host read in the one-iteration step graph */
 } GadmmChain;
 
 int gadmm_chain_half_iter(const GadmmChain* c, int color, void* stream);
