@@ -67,6 +67,8 @@ def main():
     ap.add_argument("--fo-iters", type=int, default=200, help="iteration budget of the first-order family")
     ap.add_argument("--impl", default="b200", choices=["b200", "nccl"])
     ap.add_argument("--algos", default="gadmm,dgadmm,star,gd,lagps,lagwk,iag,dgd,dualavg,dualavg_jacobi")
+    ap.add_argument("--store", default="f64", choices=["f64", "mixed"],
+                    help="chain arms: fp64 inverses, or fp32 inverses until the gap is small, then fp64")
     ap.add_argument("--out", default="")
     a = ap.parse_args()
 
@@ -105,7 +107,8 @@ def main():
     if "gadmm" in algos or "dgadmm" in algos:
         from gadmm_b200.engine.chain import ChainEngine
         from gadmm_b200.ops.topology import find_path_batch_device
-        eng = ChainEngine(N, d, a.rho, obj0, 1e-4, a.cap + 8, dist=D, dynamic="dgadmm" in algos, stop=False)
+        eng = ChainEngine(N, d, a.rho, obj0, 1e-4, a.cap + 8, dist=D, dynamic="dgadmm" in algos, stop=False,
+                          store=a.store)
         for k0, G, b, hyy in SC.worker_grams(eng.gids, d, s, dp, dev=dev):
             eng.ingest_gram(G, b, hyy, k0)
         eng._desc = None
@@ -122,7 +125,8 @@ def main():
                 it = eng.run(a.cap, window=32)
             obj, loss, it, tv = eng.results(it)
             record(D, a.out, "GADMM (static chain)" if name == "gadmm" else f"D-GADMM tau={a.tau}",
-                   "b200", loss, tv, eng.Nloc * packed_bytes, hbm, {"rho": a.rho})
+                   "b200", loss, tv, eng.Nloc * packed_bytes, hbm,
+                   {"rho": a.rho, "store": a.store, "switched_to_fp64_at": getattr(eng, "switched_at", None)})
         del eng
         free()
 
