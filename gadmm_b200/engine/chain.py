@@ -646,6 +646,7 @@ class ChainEngine:
                   self.fin_counters, self.wready, self.objw, self.obj_hist, self.loss_hist,
                   self.t_hist, self.ringcnt, self.nuflag, self.sync):
             t.zero_()
+        self.switched_at = None
         if self.mixed:                      # back to the fp32 phase
             self.store, self.P = nv.STORE_F32, self.P32
             if not self.dynamic:
