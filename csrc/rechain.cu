@@ -60,6 +60,18 @@ rechain_tables_kernel(const GadmmRechain p) {
     p.tab[5 * Nl + k] = t0;
     p.tab[6 * Nl + k] = t1;
     p.Mptr[k] = (c == 1 ? p.base_c1 : p.base_c2) + (long long)k * p.stride_bytes;
+    // Launch order of the local workers = their order along the NEW chain.  Every GPU does the
+    // same, so each phase advances as one wavefront along the chain: a tail worker early in the
+    // launch order depends on head workers that are early in their GPUs' launch order too.
+    // (Otherwise CTAs sit spinning on flags whose producers are queued behind them elsewhere.)
+    if (p.order) {
+      int rank = 0;
+      for (int j = 0; j < Nl; ++j) {
+        const int pj = p.pos[p.tab[j]];
+        rank += (pj < ps) ? 1 : 0;
+      }
+      p.order[rank] = k;
+    }
   }
   // fused peer gather of the new remote neighbours (version it-1 lives in slot (it-1)&1)
   const unsigned long long ver = it - 1ull;

@@ -422,6 +422,7 @@ class ChainEngine:
         r.stride_bytes = self.P[2].stride(0) * self.P[2].element_size()
         r.tau, r.N, r.Nloc, r.dp = tau_i, N, self.Nloc, self.dp
         r.rank, r.nranks, r.K = self.dist.rank, self.dist.world, K
+        r.order = 0 if os.environ.get("GADMM_B200_NO_REORDER") == "1" else self.order.data_ptr()
         c = self.desc()
         graphs = {}
 

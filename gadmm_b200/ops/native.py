@@ -194,5 +194,5 @@ class GadmmRechain(C.Structure):
         ("base_c1", C.c_longlong), ("base_c2", C.c_longlong), ("stride_bytes", C.c_longlong),
         ("dyn", _vp), ("tau", C.c_longlong),
         ("N", C.c_int), ("Nloc", C.c_int), ("dp", C.c_int), ("rank", C.c_int), ("nranks", C.c_int),
-        ("K", C.c_int),
+        ("K", C.c_int), ("order", _vp),
     ]

@@ -163,6 +163,7 @@ typedef struct GadmmRechain {
   const long long* dyn;      /* device [2]: window index of paths[0], number of valid rows */
   long long tau;
   int N, Nloc, dp, rank, nranks, K;
+  int* order;                /* optional [Nloc]: GadmmChain.order, rewritten to chain order on a re-chain */
 } GadmmRechain;
 int gadmm_rechain(const GadmmRechain* p, void* stream);
 
