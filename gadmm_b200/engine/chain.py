@@ -408,6 +408,11 @@ class ChainEngine:
         L.gadmm_chain_configure()
         N, dev = self.N, self.dev
         tau_i = 0 if tau >= 1e8 else int(tau)
+        if tau_i > 1:
+            # windows that are whole multiples of tau start at the same offset from a re-chain
+            # point every time, so ONE captured graph serves the whole run (a new graph per window
+            # offset would be captured inside the run, with the GPU idle meanwhile)
+            window = max(tau_i, (int(window) // tau_i) * tau_i)
         K = int(chunk)
         paths_dev = torch.zeros((K, N), dtype=torch.int32, device=dev)
         paths_host = torch.zeros((K, N), dtype=torch.int32).pin_memory()
