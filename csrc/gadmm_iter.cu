@@ -205,18 +205,25 @@ gadmm_half_iter_kernel(const GadmmChain c, const int color, const int off) {
 }
 
 // ------------------------------------------------------------------ parallel finisher (large d)
-// For d >= 512 the column-partial reduction is worth spreading over many CTAs: one CTA of 64
+// For d >= 512 the column-partial reduction is worth spreading over many CTAs: one CTA of 256
 // threads per 64-entry block of theta_n.  It waits (ld.acquire) until the streaming kernel has
 // published worker k's partials, adds them in a fixed order, writes theta (local replica + NVLink
 // P2P stores into the neighbour GPUs), and the last block of the worker folds the per-block
 // objective pieces and releases the version flags.  Launched with programmatic dependent launch
 // right behind the streaming kernel, so its CTAs fill SM slots as that kernel drains.
-__global__ void __launch_bounds__(64)
+__global__ void __launch_bounds__(256)
 gadmm_finish_kernel(const GadmmChain c, const int color, const int off) {
   __shared__ double red[8];
+  __shared__ double gpart[4][kT];
   __shared__ unsigned int ticket;
   __shared__ unsigned long long s_it;
-  const int J = blockIdx.x, k = c.order[blockIdx.y], tid = threadIdx.x;
+  // 64 * ng threads: column tid & 63; the ng groups (tid >> 6) split the tile-rows I of the column-
+  // partial sum between them.  ng = 4 for wide models (at d = 16384 a column has up to 255
+  // partials: one thread adding them all is ~25 us of dependent L2 round trips on the critical
+  // path of every phase; one worker per GPU: 0.521 -> 0.421 ms per iteration), ng = 1 otherwise
+  // (at d = 4096 the extra threads cost more than they save: 1.314 vs 1.330 ms, same-box A/B).
+  const int J = blockIdx.x, k = c.order[blockIdx.y], tid = threadIdx.x, col = tid & 63, grp = tid >> 6;
+  const int ng = blockDim.x >> 6;
   if (c.pdl) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   if (c.color[k] != color) return;
   const unsigned long long it = chain_enter(c, off, c.pdl && color == 0 && off > 0, &s_it);
@@ -237,17 +244,30 @@ gadmm_finish_kernel(const GadmmChain c, const int color, const int off) {
   const double* colpart = c.colpart + (size_t)k * colpart_elems(c.dp);
   const size_t slot_out = (size_t)(it & 1ull) * c.Nglob;
   const int p0 = c.push0[k], p1 = c.push1[k];
-  const int j = J * kT + tid;
-  const double th = symv_gather(rowpart, colpart, nT, j, c.nsplit, c.dp);
-  const double rj = xf(j);
-  c.theta[(slot_out + g) * c.dp + j] = th;
-  if (p0 >= 0) c.theta_peer[p0][(slot_out + g) * c.dp + j] = th;   // NVLink P2P stores
-  if (p1 >= 0) c.theta_peer[p1][(slot_out + g) * c.dp + j] = th;
-  const double crho = c.rho * (double)c.cmul[k];
-  double s1 = th * (rj - crho * th), s2 = xf.b[j] * th;
-  s1 = warp_sum(s1);
-  s2 = warp_sum(s2);
-  if ((tid & 31) == 0) { red[(tid >> 5) * 2] = s1; red[(tid >> 5) * 2 + 1] = s2; }
+  const int j = J * kT + col;
+  {
+    // fixed partition (I = J+1+grp, +ng, ...) and fixed combination order: deterministic
+    double v = 0.0;
+    if (grp == 0)
+      for (int q = 0; q < c.nsplit; ++q) v += __ldcg(rowpart + (size_t)q * c.dp + j);
+#pragma unroll 8
+    for (int I = J + 1 + grp; I < nT; I += ng) v += __ldcg(colpart + colpart_off(I, J) + col);
+    gpart[grp][col] = v;
+  }
+  __syncthreads();
+  double s1 = 0.0, s2 = 0.0;
+  if (grp == 0) {
+    double th = gpart[0][col];
+    for (int q = 1; q < ng; ++q) th += gpart[q][col];
+    const double rj = xf(j);
+    c.theta[(slot_out + g) * c.dp + j] = th;
+    if (p0 >= 0) c.theta_peer[p0][(slot_out + g) * c.dp + j] = th;   // NVLink P2P stores
+    if (p1 >= 0) c.theta_peer[p1][(slot_out + g) * c.dp + j] = th;
+    const double crho = c.rho * (double)c.cmul[k];
+    s1 = warp_sum(th * (rj - crho * th));
+    s2 = warp_sum(xf.b[j] * th);
+    if ((tid & 31) == 0) { red[(tid >> 5) * 2] = s1; red[(tid >> 5) * 2 + 1] = s2; }
+  }
   __syncthreads();
   if (tid == 0) {
     double* sb = c.sblk + ((size_t)k * nT + J) * 2;
@@ -257,7 +277,7 @@ gadmm_finish_kernel(const GadmmChain c, const int color, const int off) {
     ticket = atomicAdd(c.fin_counters + k, 1u);
   }
   __syncthreads();
-  if (ticket != (unsigned)(nT - 1)) return;
+  if (ticket != (unsigned)(nT - 1) || grp != 0) return;
   __threadfence();
   double a1 = 0.0, a2 = 0.0;
   for (int q = tid; q < nT; q += 64) {           // fixed partition + fixed tree: deterministic
@@ -266,9 +286,9 @@ gadmm_finish_kernel(const GadmmChain c, const int color, const int off) {
   }
   a1 = warp_sum(a1);
   a2 = warp_sum(a2);
-  __syncthreads();
+  asm volatile("bar.sync 2, 64;" ::: "memory");   // (only the 64 threads of group 0 are left)
   if ((tid & 31) == 0) { red[(tid >> 5) * 2] = a1; red[(tid >> 5) * 2 + 1] = a2; }
-  __syncthreads();
+  asm volatile("bar.sync 2, 64;" ::: "memory");
   if (tid == 0) {
     c.fin_counters[k] = 0u;
     c.objw[(size_t)(it & 1ull) * c.Nloc + k] = 0.5 * (red[0] + red[2]) - (red[1] + red[3]) + c.hyy[k];
@@ -426,7 +446,8 @@ static int launch_half(const GadmmChain* c, int color, int off, cudaStream_t st)
                    : launch_half_impl<T, S1>(c, color, off, st))
     return e;
   if (c->split_finish)
-    GADMM_CUDA_OK(launch_k(gadmm_finish_kernel, dim3(nT, c->Nloc), dim3(64), 0, st, c->pdl != 0,
+    GADMM_CUDA_OK(launch_k(gadmm_finish_kernel, dim3(nT, c->Nloc), dim3(nT >= 96 ? 256 : 64), 0, st,
+                           c->pdl != 0,
                            *c, color, off));
   return 0;
 }

@@ -38,7 +38,8 @@ def test_gadmm_reference_shape(ref_linear, rho):
 
 def test_gadmm_odd_and_tiny_chains():
     rng = np.random.default_rng(5)
-    for N, s, d in ((1, 9, 5), (2, 9, 5), (3, 9, 5), (7, 20, 66), (4, 30, 530)):
+    # (the last shape has 97 tile-rows: the finisher's four-group column reduction)
+    for N, s, d in ((1, 9, 5), (2, 9, 5), (3, 9, 5), (7, 20, 66), (4, 30, 530), (2, 12, 6200)):
         XX = rng.standard_normal((N * s, d))
         YY = rng.standard_normal(N * s)
         obj0 = O.opt_sol_closedForm(XX, YY)
