@@ -54,9 +54,29 @@ __host__ __device__ inline size_t colpart_off(int I, int J) {
 __device__ __forceinline__ double2 ld_pair(const double* p) {
   return *reinterpret_cast<const double2*>(p);
 }
+// fp32 -> fp64 widening.  The F2F.F64.F32 instruction runs on the quarter-rate XU pipe, which the
+// fp32-tile kernel loads to 34 % on average with bursts above its peak (ncu,
+// profiles/half_iter_f32_ncu_raw_r2.csv); GADMM_F2D_INT=1 does the widening with integer ops on
+// the ALU pipe instead (exact for normal numbers and zero; fp32 denormals flush to zero, which for
+// entries of an inverse matrix is below any effect).
+#ifndef GADMM_F2D_INT
+#define GADMM_F2D_INT 0
+#endif
+__device__ __forceinline__ double widen_f32(float f) {
+#if GADMM_F2D_INT
+  const unsigned int u = __float_as_uint(f);
+  const unsigned int mag = u & 0x7fffffffu;
+  unsigned int hi = (mag >> 3) + 0x38000000u;            // exponent re-biased by 1023 - 127 = 896
+  unsigned int lo = u << 29;
+  if (mag < 0x00800000u) { hi = 0u; lo = 0u; }           // zero / denormal
+  return __hiloint2double((int)(hi | (u & 0x80000000u)), (int)lo);
+#else
+  return (double)f;
+#endif
+}
 __device__ __forceinline__ double2 ld_pair(const float* p) {
   const float2 f = *reinterpret_cast<const float2*>(p);
-  return make_double2((double)f.x, (double)f.y);
+  return make_double2(widen_f32(f.x), widen_f32(f.y));
 }
 
 // Streams the CTA's tiles and writes rowpart / colpart.  Returns true (to every thread) in the
