@@ -75,12 +75,24 @@ struct ChainX {
   const double* tl;   // neighbour replicas (may be null at the chain ends)
   const double* tr;
   double rho;
-  __device__ __forceinline__ double operator()(int j) const {
-    double t = 0.0;
-    if (tl) t += __ldcg(tl + j);
-    if (tr) t += __ldcg(tr + j);
-    return fma(rho, t, b[j] - __ldcg(nu + j));   // nu is rewritten by a kernel that may overlap
+  struct Raw { double l, r, b, nu; };
+  __device__ __forceinline__ Raw load(int j) const {
+    Raw v;
+    // a missing neighbour is decided in fin(): a select here would pull the first use of the
+    // loaded value (and the wait for it) up to the load
+    v.l = __ldcg((tl ? tl : nu) + j);
+    v.r = __ldcg((tr ? tr : nu) + j);
+    v.b = b[j];
+    v.nu = __ldcg(nu + j);                       // nu is rewritten by a kernel that may overlap
+    return v;
   }
+  __device__ __forceinline__ double fin(const Raw& v) const {
+    double t = 0.0;
+    if (tl) t += v.l;
+    if (tr) t += v.r;
+    return fma(rho, t, v.b - v.nu);
+  }
+  __device__ __forceinline__ double operator()(int j) const { return fin(load(j)); }
 };
 
 // Common entry of every launch of a window: which iteration is this, and is it frozen?

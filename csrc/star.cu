@@ -41,6 +41,11 @@ struct StarWorkerX {
   __device__ __forceinline__ double operator()(int j) const {
     return b[j] - lam_new(j) + rho * z[j];
   }
+  struct Raw { double b, lam, th, z; };
+  __device__ __forceinline__ Raw load(int j) const { return Raw{b[j], lam[j], th[j], z[j]}; }
+  __device__ __forceinline__ double fin(const Raw& v) const {
+    return v.b - (v.lam + rho * (v.th - v.z)) + rho * v.z;
+  }
 };
 
 template <typename T>

@@ -13,6 +13,7 @@
 // by the finisher (the last CTA of the matrix, found with an atomic ticket) in a fixed order, so
 // results are bit-reproducible run to run.
 #pragma once
+#include <type_traits>
 #include "common.cuh"
 
 namespace gadmm {
@@ -29,6 +30,31 @@ constexpr int kBulkSplit = GADMM_BULK_SPLIT;
 template <typename T> struct SymvCfg;
 template <> struct SymvCfg<double> { static constexpr int STAGES = 3; };
 template <> struct SymvCfg<float>  { static constexpr int STAGES = 6; };
+
+// RHS functors may split into raw loads and the arithmetic on them (`Raw`, `load`, `fin`), so that
+// the producer can keep the loads of several tiles in flight; functors without the split are
+// used as they are.
+template <typename XF, typename = void> struct XSplit {
+  using Raw = double;
+  static __device__ __forceinline__ Raw load(const XF& xf, int j) { return xf(j); }
+  static __device__ __forceinline__ double fin(const XF&, const Raw& r) { return r; }
+};
+template <typename XF> struct XSplit<XF, std::void_t<typename XF::Raw>> {
+  using Raw = typename XF::Raw;
+  static __device__ __forceinline__ Raw load(const XF& xf, int j) { return xf.load(j); }
+  static __device__ __forceinline__ double fin(const XF& xf, const Raw& r) { return xf.fin(r); }
+};
+
+// Tiles per producer group (see the producer loop).
+#ifndef GADMM_XGROUP_F32
+#define GADMM_XGROUP_F32 3
+#endif
+#ifndef GADMM_XGROUP_F64
+#define GADMM_XGROUP_F64 2
+#endif
+template <typename T> struct XGroup;
+template <> struct XGroup<double> { static constexpr int G = GADMM_XGROUP_F64; };
+template <> struct XGroup<float>  { static constexpr int G = GADMM_XGROUP_F32; };
 
 template <typename T, int NSTAGES = SymvCfg<T>::STAGES>
 struct SymvSmem {
@@ -108,131 +134,79 @@ __device__ bool symv_cta(SymvSmem<T, NSTAGES>& sm, const T* __restrict__ S, int 
 
   if (warp == kConsumerWarps) {
     // ------------------------------------------------------------------ producer warp
-    // The x slices are fetched kXG tiles ahead in registers (group g+1 is in flight while the
-    // tiles of group g are issued), so the global-load latency of the fused RHS assembly never
-    // sits between two bulk copies -- that matters when a GPU has few CTAs in flight (one worker
-    // per GPU: 128 CTAs, each needing ~50 GB/s).
-// Register prefetch of the x slices one group ahead: measured 9 % SLOWER on the flagship shape
-// (1.464 vs 1.331 ms/iteration at 128 workers x d=4096 per GPU; same box A/B), so it is off.
-#ifndef GADMM_XPREFETCH
-#define GADMM_XPREFETCH 0
-#endif
-// One-deep software pipeline of the RHS slice loads (GADMM_XPIPE=1): same-box A/B at 128 workers x
-// d=4096 per GPU: fp64 tiles 1.3099 vs 1.3096 ms, fp32 tiles 0.785 vs 0.775 ms per iteration --
-// the producer is not the limiter, so it is off.  (A two-deep variant measured 1.304 / 0.780 ms
-// against 1.300 / 0.766 ms on another box: same conclusion.)
-#ifndef GADMM_XPIPE
-#define GADMM_XPIPE 0
-#endif
-    constexpr int kXG = 4;
-    int stage = 0;
-    uint32_t phase = 0;
-#if GADMM_XPIPE
-    // One-deep software pipeline over the tiles of BOTH tile-rows: the bulk copy of tile t and the
-    // global loads of its RHS slice are issued first, then the slice of tile t-1 (whose loads
-    // have had a whole tile period to land) is written to shared memory and tile t-1 is handed
-    // to the consumers.  Without it every tile costs one L2 round trip of the fused RHS assembly
-    // between two bulk copies (~0.8 us): harmless with 32 KiB fp64 tiles, but it caps a CTA at
-    // ~20 GB/s with 16 KiB fp32 tiles.
+    // Per tile the producer has to (a) wait for a free stage and issue the bulk copy and (b)
+    // assemble the RHS slice x_J (xf: a few global loads + arithmetic, one L2 round trip) and
+    // hand the stage to the consumers.  Done tile by tile, the round trip of (b) is the
+    // producer's whole period: ncu on the fp32 instantiation showed it spending half of its time
+    // there, almost none waiting for a free stage, and the consumers 26 % of theirs on the
+    // `full` barriers (profiles/half_iter_fp64.md).  So the tiles of both tile-rows form one flat
+    // sequence that is processed in groups of G: the raw loads of a whole group are issued back
+    // to back (one round trip per group), then, tile by tile, the bulk copy of the tile one group
+    // AHEAD is issued and the tile of this group is handed off -- the arithmetic on the raw
+    // values sits behind the (asm volatile) stage wait, so the loads are in flight while the next
+    // copies are issued and the ring stays full.  G <= STAGES - 1: issuing tile t + G needs the
+    // stage of tile t + G - STAGES back, which must have been handed off already.
+    //
+    // History (same-box A/Bs at 128 workers x d=4096 per GPU, ms per iteration fp64 / fp32 tiles):
+    //   tile by tile                                   1.3026 / 0.7765
+    //   register prefetch of computed slices, 4 ahead  9 % slower (fp64)
+    //   one- / two-deep pipelining of COMPUTED slices  neutral (the compiler keeps the arithmetic,
+    //                                                  hence the stall, next to the loads)
+    //   groups of 3 (fp32) / 2 (fp64), no look-ahead   1.2970 / 0.7374
+    using XS = XSplit<XF>;
+    using Raw = typename XS::Raw;
+    constexpr int G = XGroup<T>::G < STAGES - 1 ? XGroup<T>::G : STAGES - 1;
+    const int JbA = (int)(((long long)(rowA + 1) * part) / nparts);
+    const int JeA = (int)(((long long)(rowA + 1) * (part + 1)) / nparts);
+    const int JbB = (int)(((long long)(rowB + 1) * part) / nparts);
+    const int JeB = (int)(((long long)(rowB + 1) * (part + 1)) / nparts);
+    const int nA = JeA - JbA;
+    const int total = nA + (nrows == 2 ? JeB - JbB : 0);
+    const T* baseA = S + ((size_t)rowA * (rowA + 1) / 2) * (kT * kT);
+    const T* baseB = S + ((size_t)rowB * (rowB + 1) / 2) * (kT * kT);
+    int istage = 0;            // ring position of the next bulk copy
+    uint32_t iphase = 0;
+    int hstage = 0;            // ring position of the next hand-off
+    auto issue = [&](int t) {
+      const T* src = t < nA ? baseA + (size_t)(JbA + t) * (kT * kT)
+                            : baseB + (size_t)(JbB + t - nA) * (kT * kT);
+      mbar_wait(&sm.empty[istage], iphase ^ 1);
+      if (lane == 0) bulk_g2s(sm.tile[istage], src, kTileBytes, &sm.full[istage]);
+      if (++istage == STAGES) { istage = 0; iphase ^= 1; }
+    };
+#pragma unroll
+    for (int g = 0; g < G; ++g)
+      if (g < total) issue(g);
     {
-      double pend0 = 0.0, pend1 = 0.0;
-      int pend_stage = -1;
-      for (int rr = 0; rr < nrows; ++rr) {
-        const int I = rr == 0 ? rowA : rowB;
-        const int Jb = (int)(((long long)(I + 1) * part) / nparts);
-        const int Je = (int)(((long long)(I + 1) * (part + 1)) / nparts);
-        sm.xrow[rr][lane] = xf(I * kT + lane);
-        sm.xrow[rr][lane + 32] = xf(I * kT + lane + 32);
-        const T* rowbase = S + ((size_t)I * (I + 1) / 2) * (kT * kT);
-        for (int J = Jb; J < Je; ++J) {
-          mbar_wait(&sm.empty[stage], phase ^ 1);
-          if (lane == 0) bulk_g2s(sm.tile[stage], rowbase + (size_t)J * (kT * kT), kTileBytes, &sm.full[stage]);
-          const double x0 = xf(J * kT + lane), x1 = xf(J * kT + lane + 32);   // in flight
-          if (pend_stage >= 0) {
-            sm.xs[pend_stage][lane] = pend0;
-            sm.xs[pend_stage][lane + 32] = pend1;
-            __syncwarp();
-            if (lane == 0) mbar_arrive_expect_tx(&sm.full[pend_stage], kTileBytes);
-          }
-          pend0 = x0;
-          pend1 = x1;
-          pend_stage = stage;
-          if (++stage == STAGES) { stage = 0; phase ^= 1; }
-        }
-      }
-      if (pend_stage >= 0) {
-        sm.xs[pend_stage][lane] = pend0;
-        sm.xs[pend_stage][lane + 32] = pend1;
-        __syncwarp();
-        if (lane == 0) mbar_arrive_expect_tx(&sm.full[pend_stage], kTileBytes);
-      }
+      // x_I slices for the column products of the two tile-rows (read after the first `full`)
+      const Raw a0 = XS::load(xf, rowA * kT + lane), a1 = XS::load(xf, rowA * kT + lane + 32);
+      const Raw b0 = XS::load(xf, rowB * kT + lane), b1 = XS::load(xf, rowB * kT + lane + 32);
+      sm.xrow[0][lane] = XS::fin(xf, a0);
+      sm.xrow[0][lane + 32] = XS::fin(xf, a1);
+      sm.xrow[1][lane] = XS::fin(xf, b0);
+      sm.xrow[1][lane + 32] = XS::fin(xf, b1);
     }
-#elif !GADMM_XPREFETCH
-    for (int rr = 0; rr < nrows; ++rr) {
-      const int I = rr == 0 ? rowA : rowB;
-      const int Jb = (int)(((long long)(I + 1) * part) / nparts);
-      const int Je = (int)(((long long)(I + 1) * (part + 1)) / nparts);
-      sm.xrow[rr][lane] = xf(I * kT + lane);
-      sm.xrow[rr][lane + 32] = xf(I * kT + lane + 32);
-      const T* rowbase = S + ((size_t)I * (I + 1) / 2) * (kT * kT);
-      for (int J = Jb; J < Je; ++J) {
-        mbar_wait(&sm.empty[stage], phase ^ 1);
-        if (lane == 0) bulk_g2s(sm.tile[stage], rowbase + (size_t)J * (kT * kT), kTileBytes, &sm.full[stage]);
-        sm.xs[stage][lane] = xf(J * kT + lane);
-        sm.xs[stage][lane + 32] = xf(J * kT + lane + 32);
-        __syncwarp();
-        if (lane == 0) mbar_arrive_expect_tx(&sm.full[stage], kTileBytes);
-        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+    for (int t0 = 0; t0 < total; t0 += G) {
+      Raw raw[G][2];
+#pragma unroll
+      for (int g = 0; g < G; ++g) {
+        const int t = min(t0 + g, total - 1);    // clamped, not predicated: the loads must stay
+        const int J = t < nA ? JbA + t : JbB + t - nA;   // branch-free to be issued back to back
+        raw[g][0] = XS::load(xf, J * kT + lane);
+        raw[g][1] = XS::load(xf, J * kT + lane + 32);
       }
-    }
-#else
-    for (int rr = 0; rr < nrows; ++rr) {
-      const int I = rr == 0 ? rowA : rowB;
-      const int Jb = (int)(((long long)(I + 1) * part) / nparts);
-      const int Je = (int)(((long long)(I + 1) * (part + 1)) / nparts);     // tiles [Jb, Je)
-      double cur[2 * kXG], nxt[2 * kXG];
 #pragma unroll
-      for (int q = 0; q < kXG; ++q) {
-        const bool ok = Jb + q < Je;
-        nxt[2 * q] = ok ? xf((Jb + q) * kT + lane) : 0.0;
-        nxt[2 * q + 1] = ok ? xf((Jb + q) * kT + lane + 32) : 0.0;
-      }
-      // x_I slice for the column products of this tile-row
-      sm.xrow[rr][lane] = xf(I * kT + lane);
-      sm.xrow[rr][lane + 32] = xf(I * kT + lane + 32);
-      const T* rowbase = S + ((size_t)I * (I + 1) / 2) * (kT * kT);
-      for (int J0 = Jb; J0 < Je; J0 += kXG) {
-#pragma unroll
-        for (int q = 0; q < 2 * kXG; ++q) cur[q] = nxt[q];
-#pragma unroll
-        for (int q = 0; q < kXG; ++q) {            // prefetch the next group's slices
-          const int Jn = J0 + kXG + q;
-          const bool ok = Jn < Je;
-          nxt[2 * q] = ok ? xf(Jn * kT + lane) : 0.0;
-          nxt[2 * q + 1] = ok ? xf(Jn * kT + lane + 32) : 0.0;
-        }
-#pragma unroll
-        for (int q = 0; q < kXG; ++q) {
-          const int J = J0 + q;
-          if (J >= Je) break;
-          mbar_wait(&sm.empty[stage], phase ^ 1);
-          // one tile = kBulkSplit bulk copies issued by different lanes: copies issued by one
-          // thread were observed to execute back to back (~25 GB/s per CTA), which starves
-          // phases with few CTAs per GPU; independent issuers overlap
-          if (lane < kBulkSplit)
-            bulk_g2s(reinterpret_cast<unsigned char*>(sm.tile[stage]) + lane * (kTileBytes / kBulkSplit),
-                     reinterpret_cast<const unsigned char*>(rowbase + (size_t)J * (kT * kT)) +
-                         lane * (kTileBytes / kBulkSplit),
-                     kTileBytes / kBulkSplit, &sm.full[stage]);
-          sm.xs[stage][lane] = cur[2 * q];
-          sm.xs[stage][lane + 32] = cur[2 * q + 1];
+      for (int g = 0; g < G; ++g) {
+        if (t0 + G + g < total) issue(t0 + G + g);
+        if (t0 + g < total) {
+          sm.xs[hstage][lane] = XS::fin(xf, raw[g][0]);
+          sm.xs[hstage][lane + 32] = XS::fin(xf, raw[g][1]);
           __syncwarp();
-          if (lane == 0) mbar_arrive_expect_tx(&sm.full[stage], kTileBytes);
-          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+          if (lane == 0) mbar_arrive_expect_tx(&sm.full[hstage], kTileBytes);
+          if (++hstage == STAGES) hstage = 0;
         }
       }
     }
-#endif
   } else {
     // ------------------------------------------------------------------ consumer warps
     int stage = 0;
