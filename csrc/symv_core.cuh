@@ -22,10 +22,7 @@ constexpr int kT = GADMM_TILE;           // 64
 constexpr int kConsumerWarps = 8;
 constexpr int kSymvThreads = (kConsumerWarps + 1) * 32;  // 288
 constexpr int kRowsPerWarp = kT / kConsumerWarps;        // 8
-#ifndef GADMM_BULK_SPLIT
-#define GADMM_BULK_SPLIT 1      // splitting a tile over several issuing lanes made no difference
-#endif
-constexpr int kBulkSplit = GADMM_BULK_SPLIT;
+// (One bulk copy per tile: splitting a tile over several issuing lanes made no difference.)
 
 template <typename T> struct SymvCfg;
 template <> struct SymvCfg<double> { static constexpr int STAGES = 3; };

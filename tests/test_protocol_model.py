@@ -439,3 +439,74 @@ def test_dgd_halo_with_backpressure_is_safe_and_without_is_caught():
     assert bad is None, bad
     _, bad = _explore_dgd(5, backpressure=False)
     assert bad is not None and bad[0] != "deadlock"       # reads the row of iteration it+1
+
+
+# ------------------------------------------------------------------------------------------------
+# Tile ring of the streaming SYMV (csrc/symv_core.cuh, producer loop): the producer warp issues the
+# bulk copy of a tile one GROUP ahead of the tile it hands to the consumers.  Model: the producer
+# runs the op list of the loop, the copy engine completes issued copies in any order, the
+# consumers take the tiles in order.  Checked: no deadlock, no stage (tile buffer or RHS slice)
+# overwritten before its previous tile was consumed, the consumers see tile t in stage t % STAGES.
+def _producer_ops(total: int, G: int):
+    ops = [("issue", g) for g in range(min(G, total))]
+    for t0 in range(0, total, G):
+        for g in range(G):
+            if t0 + G + g < total:
+                ops.append(("issue", t0 + G + g))
+            if t0 + g < total:
+                ops.append(("hand", t0 + g))
+    return ops
+
+
+def _explore_tile_ring(total: int, stages: int, G: int):
+    ops = _producer_ops(total, G)
+    # state: producer pc, frozenset of copies in flight, per-stage (tile whose data landed or -1),
+    # per-stage (tile whose slice was written or -1), consumed count
+    init = (0, frozenset(), (-1,) * stages, (-1,) * stages, 0)
+    seen = {init}
+    stack = [init]
+    while stack:
+        pc, flight, data, xs, done = stack.pop()
+        succ = []
+        if pc < len(ops):
+            kind, t = ops[pc]
+            s = t % stages
+            if kind == "issue":
+                if t < stages or done > t - stages:          # empty[s] of the previous user
+                    succ.append((pc + 1, flight | {t}, data, xs, done))
+            else:
+                if xs[s] >= 0 and done <= xs[s]:             # slice of an unconsumed tile
+                    return len(seen), ("slice overwritten", t, xs[s])
+                succ.append((pc + 1, flight, data, tuple(t if q == s else xs[q] for q in range(stages)), done))
+        for t in flight:                                     # a copy lands
+            s = t % stages
+            if data[s] >= 0 and done <= data[s]:
+                return len(seen), ("tile overwritten", t, data[s])
+            succ.append((pc, flight - {t}, tuple(t if q == s else data[q] for q in range(stages)), xs, done))
+        if done < total:                                     # consumers: full[s] = copy landed + hand-off
+            s = done % stages
+            if data[s] == done and xs[s] == done:
+                succ.append((pc, flight, data, xs, done + 1))
+            elif data[s] > done or xs[s] > done:
+                return len(seen), ("wrong tile in stage", done, data[s], xs[s])
+        if not succ and (done < total or pc < len(ops)):
+            return len(seen), ("deadlock", pc, done)
+        for st in succ:
+            if st not in seen:
+                seen.add(st)
+                stack.append(st)
+    return len(seen), None
+
+
+@pytest.mark.parametrize("stages,G", [(3, 1), (3, 2), (6, 3), (6, 5), (12, 3)])
+@pytest.mark.parametrize("total", [0, 1, 2, 7, 13])
+def test_tile_ring_with_lookahead_is_safe(total, stages, G):
+    _, bad = _explore_tile_ring(total, stages, G)
+    assert bad is None, bad
+
+
+def test_tile_ring_group_as_deep_as_the_ring_deadlocks():
+    # issuing tile t + G needs the stage of tile t + G - STAGES back, i.e. G <= STAGES - 1
+    # (the kernel clamps G accordingly)
+    _, bad = _explore_tile_ring(9, 3, 3)
+    assert bad is not None and bad[0] == "deadlock"
