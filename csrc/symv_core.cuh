@@ -6,7 +6,8 @@
 //
 // CTA structure (288 threads): warp 8 is the producer -- it streams tiles global -> shared with
 // cp.async.bulk (UBLKCP) through a STAGES-deep mbarrier ring and assembles the matching 64-entry
-// slice of x (the fused RHS) beside every tile; warps 0..7 are consumers -- warp w owns rows
+// slice of x (the fused RHS) beside every tile, a group of tiles at a time with the bulk copies
+// running one group ahead (see the producer loop); warps 0..7 are consumers -- warp w owns rows
 // 8w..8w+7 of every tile, lane l owns columns 2l,2l+1.  Per element: one FMA into the row sum
 // (y_I += T x_J) and one into the column sum (y_J += T' x_I), all in fp64, no shuffles in the
 // inner loop.  Row sums are finished inside the CTA; column sums go to `colpart` and are added
@@ -77,11 +78,11 @@ __host__ __device__ inline size_t colpart_off(int I, int J) {
 __device__ __forceinline__ double2 ld_pair(const double* p) {
   return *reinterpret_cast<const double2*>(p);
 }
-// fp32 -> fp64 widening.  The F2F.F64.F32 instruction runs on the quarter-rate XU pipe, which the
-// fp32-tile kernel loads to 34 % on average with bursts above its peak (ncu,
-// profiles/half_iter_f32_ncu_raw_r2.csv); GADMM_F2D_INT=1 does the widening with integer ops on
-// the ALU pipe instead (exact for normal numbers and zero; fp32 denormals flush to zero, which for
-// entries of an inverse matrix is below any effect).
+// fp32 -> fp64 widening.  F2F.F64.F32 runs on the quarter-rate XU pipe, the busiest pipe of the
+// fp32-tile kernel (34 %, ncu: profiles/half_iter_f32_ncu_raw_r2.csv).  GADMM_F2D_INT=1 widens with
+// integer ops on the ALU pipe instead (exact for normal numbers and zero, fp32 denormals flush to
+// zero); measured 4.4 % SLOWER in a same-box A/B, so it is off: the kernel was starved by its
+// producer, not bound by a pipe (profiles/half_iter_fp64.md).
 #ifndef GADMM_F2D_INT
 #define GADMM_F2D_INT 0
 #endif
